@@ -1,0 +1,111 @@
+/* spectavi_b200.h -- C ABI of libspectavi.so (B200 build of spectavi's
+ * descriptor-matching path).
+ *
+ * Part 1 is the DROP-IN boundary: the same symbols, argument order and output
+ * protocol as the reference's extern "C" functions for this path, so that
+ * spectavi/feature.py's ctypes bindings (reference spectavi/feature.py:208-243,
+ * 346-358) work unchanged against this library.  All of them take HOST
+ * pointers, return void, and -- like the reference, whose failures are C++
+ * exceptions escaping extern "C" -- print one line to stderr and abort() on a
+ * violated precondition or a CUDA/NCCL error.  There is no CPU fallback.
+ *
+ * Part 2 is the device-resident API the drop-in functions are built from; it
+ * takes DEVICE pointers and a CUDA stream, returns 0 or a negative error code,
+ * and is what bench.py times with inputs already in HBM and what the
+ * one-process-per-GPU (torchrun) path shards the train set with.
+ */
+#ifndef SPECTAVI_B200_H
+#define SPECTAVI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+/* ------------------------------------------------------------------ NdArray
+ * Byte-for-byte the reference's struct (ctypes_ndarray/src/NdArray.h:17-29;
+ * Python mirror ctypes_ndarray/cndarray/ndarray.py:50-58).  Output memory is
+ * allocated by, and owned by, the caller through m_alloc. */
+typedef char *NumpyAllocator(size_t nbytes);
+typedef void SetDtypeFunc(const char *newdtype);
+
+struct NdArray {
+  char *m_data;
+  int m_ndim;
+  uint64_t *m_shape;
+  int m_sizeofdtype;
+  NumpyAllocator *m_alloc;
+  NumpyAllocator *m_realloc;
+  SetDtypeFunc *m_set_dtype;
+  char *m_dtype;
+};
+typedef struct NdArray NdArray;
+
+/* ============================ Part 1: drop-in entry points (host pointers) */
+
+/* replaces src/Spectavi.cpp:284-298 (BruteForceNnL1K2, src/BruteForceNnL1K2.h).
+ * x: xrows x dim uint8 train rows, y: yrows x dim uint8 query rows, row-major,
+ * dim % 16 == 0.  outidx: yrows x 2 size_t, outdist: yrows x 2 int32: the two
+ * lexicographically smallest (dist, idx); missing = ((size_t)-1, INT_MAX).
+ * nthreads (an OpenMP thread count in the reference) is accepted and ignored. */
+void nn_bruteforcel1k2(const uint8_t *x, const uint8_t *y, int xrows, int yrows, int dim, int nthreads,
+                       NdArray *outidx, NdArray *outdist);
+
+/* replaces src/Spectavi.cpp:258-269 (BruteForceNn<float>, src/BruteForceNn.h:37-120).
+ * k nearest under sum |d|^p (p == 1, 2, .5 special-cased, otherwise powf);
+ * outidx yrows x k size_t, outdist yrows x k float32, ascending.  mu != 0 (the
+ * reference's approximate prune) is accepted and computed exactly. */
+void nn_bruteforce(const float *x, const float *y, int xrows, int yrows, int dim, int k, float p, float mu,
+                   NdArray *outidx, NdArray *outdist);
+
+/* replaces src/Spectavi.cpp:271-282 (BruteForceNn<int>): int32 rows, per-term
+ * value truncated to int as the reference's Scalar cast does; outdist int32. */
+void nn_bruteforcei(const int *x, const int *y, int xrows, int yrows, int dim, int k, float p, float mu,
+                    NdArray *outidx, NdArray *outdist);
+
+/* replaces src/Spectavi.cpp:321-336 (CascadingHashNn, src/CascadingHashNn.h).
+ * x, y float32 holding integers in [-128,127]; outputs yrows x k (k >= 2; only
+ * columns 0,1 are written), outdist float32.  The hash dictionary is drawn
+ * from a fixed seed (env SPECTAVI_SEED overrides) instead of random_device. */
+void nn_cascading_hash(const float *x, const float *y, int xrows, int yrows, int dim, int k, int hash_bit_rate,
+                       int num_hash_tables, int num_candidate_neighbours, NdArray *outidx, NdArray *outdist);
+
+/* ============================ Part 2: device-resident API (device pointers)
+ * Results live in a KEY buffer: uint64 keys[2][yrows], key = dist << 32 | idx,
+ * all-ones = none; unsigned order of keys == the reference's (dist, idx) rule. */
+
+/* keys <- all "none" */
+int spv_keys_reset(uint64_t *dkeys, int yrows, void *stream);
+/* K1: fold the L1 top-2 of dy against dx[0..xrows) into dkeys; reported index
+ * = xoffset + local row (train shards of one query set fold into one buffer). */
+int spv_l1k2_device(const uint8_t *dx, const uint8_t *dy, int xrows, int yrows, int dim, uint32_t xoffset,
+                    uint64_t *dkeys, void *stream);
+/* K5: dkeys <- top-2 of dkeys and nsrc more key buffers laid end to end
+ * (what an all-gather of per-GPU key buffers produces). */
+int spv_keys_merge(uint64_t *dkeys, const uint64_t *dsrc, int nsrc, int yrows, void *stream);
+/* keys -> the reference's output arrays (device): idx yrows x kcols uint64,
+ * dist yrows x kcols int32 / float32 */
+int spv_keys_finalize_i32(const uint64_t *dkeys, int yrows, int kcols, uint64_t *didx, int32_t *ddist, void *stream);
+int spv_keys_finalize_f32(const uint64_t *dkeys, int yrows, int kcols, uint64_t *didx, float *ddist, void *stream);
+
+/* number of kernels this library has launched since it was loaded */
+uint64_t spv_launch_count(void);
+/* last error text of the calling thread's most recent failed spv_* call */
+const char *spv_last_error(void);
+/* packed-SAD issue-rate microbenchmark (roofline denominator; pipe_peak.cu) */
+int spv_pipe_peak(int device, int iters, double *out, const char **names, double *lanes_per_op);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPECTAVI_B200_H */

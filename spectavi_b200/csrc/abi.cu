@@ -1,0 +1,128 @@
+// abi.cu -- the extern "C" boundary of libspectavi.so (include/spectavi_b200.h).
+//
+// Part 1 mirrors reference src/Spectavi.cpp:258-298,321-336 call for call:
+// size both outputs, let the CALLER allocate them through the NdArray callback
+// (ctypes_ndarray/src/NdArray.h:41-45,67-73) from the calling thread, run the
+// matcher, write the results into the caller's memory.  What differs is where
+// the matcher runs: inputs are copied to the GPU(s), the sm_100a kernels of
+// l1_top2.cu / lp_topk.cu / cascade.cu do the work, the yrows x k results come
+// back.  There is no CPU implementation behind these symbols.
+#include "../../include/spectavi_b200.h"
+#include "spv_common.h"
+#include "host_ctx.h"
+
+#include <cstdarg>
+#include <cstdlib>
+#include <cstring>
+
+namespace spv {
+
+thread_local char g_err[512] = "";
+
+int fail(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return -1;
+}
+
+[[noreturn]] void die(const char* fn, const char* fmt, ...) {
+  // the reference's error convention on this path is an exception escaping
+  // extern "C" (BruteForceNnL1K2.h:74-81) => terminate; keep it observable.
+  char msg[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(msg, sizeof(msg), fmt, ap);
+  va_end(ap);
+  fprintf(stderr, "libspectavi(b200): %s: %s\n", fn, msg);
+  fflush(stderr);
+  abort();
+}
+
+void out_alloc(NdArray* arr, uint64_t d0, uint64_t d1) {
+  // ndarray_set_size + ndarray_alloc (NdArray.h:41-45,67-73)
+  arr->m_ndim = 2;
+  arr->m_shape[0] = d0;
+  arr->m_shape[1] = d1;
+  arr->m_data = arr->m_alloc((size_t)arr->m_sizeofdtype * d0 * d1);
+}
+
+}  // namespace spv
+
+using namespace spv;
+
+#define CU_OR_FAIL(expr)                                                             \
+  do {                                                                               \
+    cudaError_t e_ = (expr);                                                         \
+    if (e_ != cudaSuccess) return fail("%s: %s", #expr, cudaGetErrorString(e_));     \
+  } while (0)
+
+extern "C" {
+
+// ----------------------------------------------------------------- Part 2
+int spv_keys_reset(uint64_t* dkeys, int yrows, void* stream) {
+  CU_OR_FAIL(keys_reset(reinterpret_cast<unsigned long long*>(dkeys), yrows, (cudaStream_t)stream));
+  return 0;
+}
+
+int spv_l1k2_device(const uint8_t* dx, const uint8_t* dy, int xrows, int yrows, int dim, uint32_t xoffset,
+                    uint64_t* dkeys, void* stream) {
+  if (xrows < 0 || yrows < 0) return fail("negative row count");
+  if (dim <= 0 || dim % 16 != 0) return fail("dim (%d) must be a positive multiple of 16", dim);
+  CU_OR_FAIL(l1_top2_u8(dx, dy, xrows, yrows, dim, xoffset, reinterpret_cast<unsigned long long*>(dkeys),
+                        (cudaStream_t)stream));
+  return 0;
+}
+
+int spv_keys_merge(uint64_t* dkeys, const uint64_t* dsrc, int nsrc, int yrows, void* stream) {
+  CU_OR_FAIL(keys_merge(reinterpret_cast<unsigned long long*>(dkeys), reinterpret_cast<const unsigned long long*>(dsrc),
+                        nsrc, yrows, (cudaStream_t)stream));
+  return 0;
+}
+
+int spv_keys_finalize_i32(const uint64_t* dkeys, int yrows, int kcols, uint64_t* didx, int32_t* ddist, void* stream) {
+  if (kcols < 1) return fail("kcols must be >= 1");
+  CU_OR_FAIL(keys_finalize_i32(reinterpret_cast<const unsigned long long*>(dkeys), yrows, kcols, didx, ddist,
+                               (cudaStream_t)stream));
+  return 0;
+}
+
+int spv_keys_finalize_f32(const uint64_t* dkeys, int yrows, int kcols, uint64_t* didx, float* ddist, void* stream) {
+  if (kcols < 1) return fail("kcols must be >= 1");
+  CU_OR_FAIL(keys_finalize_f32(reinterpret_cast<const unsigned long long*>(dkeys), yrows, kcols, didx, ddist,
+                               (cudaStream_t)stream));
+  return 0;
+}
+
+uint64_t spv_launch_count(void) { return launches(); }
+const char* spv_last_error(void) { return g_err; }
+
+// ----------------------------------------------------------------- Part 1
+void nn_bruteforcel1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, int nthreads,
+                       NdArray* outidx, NdArray* outdist) {
+  (void)nthreads;  // OpenMP thread count in the reference (BruteForceNnL1K2.h:92); no meaning here
+  const int K = 2;
+  out_alloc(outidx, (uint64_t)yrows, K);    // Spectavi.cpp:288-291: both outputs first, on the calling thread
+  out_alloc(outdist, (uint64_t)yrows, K);
+  // BruteForceNnL1K2.h:71-82 throws on these
+  if (dim % 16 != 0) die("nn_bruteforcel1k2", "data dimension (%d) must be a multiple of 16", dim);
+  if (xrows < 0 || yrows < 0 || dim <= 0) die("nn_bruteforcel1k2", "bad shape %d x %d x %d", xrows, yrows, dim);
+  if (yrows == 0) return;
+  HostCall hc("nn_bruteforcel1k2");
+  hc.l1k2(x, y, xrows, yrows, dim, reinterpret_cast<uint64_t*>(outidx->m_data),
+          reinterpret_cast<int32_t*>(outdist->m_data));
+}
+
+// K1f / cascade entry points: filled in by lp_topk.cu / cascade.cu
+void nn_bruteforce(const float*, const float*, int, int, int, int, float, float, NdArray*, NdArray*) {
+  die("nn_bruteforce", "not built yet");
+}
+void nn_bruteforcei(const int*, const int*, int, int, int, int, float, float, NdArray*, NdArray*) {
+  die("nn_bruteforcei", "not built yet");
+}
+void nn_cascading_hash(const float*, const float*, int, int, int, int, int, int, int, NdArray*, NdArray*) {
+  die("nn_cascading_hash", "not built yet");
+}
+
+}  // extern "C"

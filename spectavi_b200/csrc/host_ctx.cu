@@ -1,0 +1,182 @@
+// host_ctx.cu -- see host_ctx.h.
+#include "host_ctx.h"
+#include "spv_common.h"
+
+#include <dlfcn.h>
+#include <nccl.h>   // types only; the library is dlopen()ed when SPECTAVI_GPUS > 1
+
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+namespace spv {
+namespace {
+
+std::mutex g_mu;
+
+struct Buf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = n + n / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+};
+
+struct Gpu {
+  int dev = -1;
+  cudaStream_t stream = nullptr;
+  Buf x, y, keys, gather, oidx, odist;
+};
+
+struct Nccl {
+  void* lib = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  std::vector<ncclComm_t> comms;
+};
+
+struct Runtime {
+  std::vector<Gpu> gpus;
+  Nccl nccl;
+  bool ready = false;
+};
+Runtime g_rt;
+
+#define CU(fn, expr)                                                     \
+  do {                                                                   \
+    cudaError_t e_ = (expr);                                             \
+    if (e_ != cudaSuccess) die(fn, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+#define NC(fn, expr)                                                     \
+  do {                                                                   \
+    ncclResult_t r_ = (expr);                                            \
+    if (r_ != ncclSuccess) die(fn, "%s: %s", #expr, g_rt.nccl.GetErrorString ? g_rt.nccl.GetErrorString(r_) : "nccl error"); \
+  } while (0)
+
+void load_nccl(const char* fn, int ngpu) {
+  Nccl& n = g_rt.nccl;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* nm : names) {
+    n.lib = dlopen(nm, RTLD_NOW | RTLD_LOCAL);
+    if (n.lib) break;
+  }
+  if (!n.lib) die(fn, "SPECTAVI_GPUS=%d needs NCCL, dlopen(libnccl.so.2) failed: %s", ngpu, dlerror());
+#define SYM(field, name)                                                  \
+  n.field = reinterpret_cast<decltype(n.field)>(dlsym(n.lib, name));      \
+  if (!n.field) die(fn, "NCCL symbol %s missing", name);
+  SYM(CommInitAll, "ncclCommInitAll") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
+  SYM(AllGather, "ncclAllGather") SYM(Broadcast, "ncclBroadcast") SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+  std::vector<int> devs(ngpu);
+  for (int g = 0; g < ngpu; ++g) devs[g] = g_rt.gpus[g].dev;
+  n.comms.resize(ngpu);
+  NC(fn, n.CommInitAll(n.comms.data(), ngpu, devs.data()));
+}
+
+void init_runtime(const char* fn) {
+  if (g_rt.ready) return;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev < 1)
+    die(fn, "no CUDA device (%s); this library has no CPU implementation", cudaGetErrorString(e));
+  int want = 1;
+  if (const char* s = getenv("SPECTAVI_GPUS")) {
+    want = (strcmp(s, "all") == 0) ? ndev : atoi(s);
+    if (want < 1 || want > ndev) die(fn, "SPECTAVI_GPUS=%s but %d device(s) visible", s, ndev);
+  }
+  int first = 0;
+  cudaGetDevice(&first);   // respect the caller's current device for the 1-GPU case
+  g_rt.gpus.resize(want);
+  for (int g = 0; g < want; ++g) {
+    Gpu& G = g_rt.gpus[g];
+    G.dev = (want == 1) ? first : g;
+    CU(fn, cudaSetDevice(G.dev));
+    CU(fn, cudaStreamCreateWithFlags(&G.stream, cudaStreamNonBlocking));
+  }
+  if (want > 1) load_nccl(fn, want);
+  CU(fn, cudaSetDevice(g_rt.gpus[0].dev));
+  g_rt.ready = true;
+}
+
+}  // namespace
+
+HostCall::HostCall(const char* fn) : fn_(fn), lock_(g_mu) { init_runtime(fn); }
+HostCall::~HostCall() {}
+
+void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist) {
+  const int G = (int)g_rt.gpus.size();
+  const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
+  const int per = (xrows + G - 1) / G;   // train rows per GPU
+  int prev = 0;
+  cudaGetDevice(&prev);
+  // stage inputs: query rows to GPU 0 (broadcast below), train shard g to GPU g
+  for (int g = 0; g < G; ++g) {
+    Gpu& D = g_rt.gpus[g];
+    CU(fn_, cudaSetDevice(D.dev));
+    const int x0 = g * per < xrows ? g * per : xrows;
+    const int xn = (x0 + per <= xrows) ? per : xrows - x0;
+    CU(fn_, D.y.ensure(ybytes));
+    CU(fn_, D.keys.ensure(kbytes));
+    if (xn > 0) {
+      CU(fn_, D.x.ensure((size_t)xn * dim));
+      CU(fn_, cudaMemcpyAsync(D.x.p, x + (size_t)x0 * dim, (size_t)xn * dim, cudaMemcpyHostToDevice, D.stream));
+    }
+    if (g == 0) CU(fn_, cudaMemcpyAsync(D.y.p, y, ybytes, cudaMemcpyHostToDevice, D.stream));
+    CU(fn_, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
+  }
+  if (G > 1) {
+    NC(fn_, g_rt.nccl.GroupStart());
+    for (int g = 0; g < G; ++g)
+      NC(fn_, g_rt.nccl.Broadcast(g_rt.gpus[0].y.p, g_rt.gpus[g].y.p, ybytes, ncclUint8, 0, g_rt.nccl.comms[g],
+                                  g_rt.gpus[g].stream));
+    NC(fn_, g_rt.nccl.GroupEnd());
+  }
+  // K1 on every shard
+  for (int g = 0; g < G; ++g) {
+    Gpu& D = g_rt.gpus[g];
+    const int x0 = g * per < xrows ? g * per : xrows;
+    const int xn = (x0 + per <= xrows) ? per : xrows - x0;
+    CU(fn_, cudaSetDevice(D.dev));
+    CU(fn_, l1_top2_u8((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, (uint32_t)x0,
+                       (unsigned long long*)D.keys.p, D.stream));
+  }
+  Gpu& R = g_rt.gpus[0];
+  if (G > 1) {
+    // all-gather the per-GPU key buffers, K5 merge on GPU 0
+    for (int g = 0; g < G; ++g) {
+      CU(fn_, cudaSetDevice(g_rt.gpus[g].dev));
+      CU(fn_, g_rt.gpus[g].gather.ensure(kbytes * G));
+    }
+    NC(fn_, g_rt.nccl.GroupStart());
+    for (int g = 0; g < G; ++g)
+      NC(fn_, g_rt.nccl.AllGather(g_rt.gpus[g].keys.p, g_rt.gpus[g].gather.p, (size_t)2 * yrows, ncclUint64,
+                                  g_rt.nccl.comms[g], g_rt.gpus[g].stream));
+    NC(fn_, g_rt.nccl.GroupEnd());
+    CU(fn_, cudaSetDevice(R.dev));
+    CU(fn_, keys_merge((unsigned long long*)R.keys.p, (const unsigned long long*)R.gather.p, G, yrows, R.stream));
+  }
+  CU(fn_, cudaSetDevice(R.dev));
+  CU(fn_, R.oidx.ensure((size_t)yrows * 2 * sizeof(uint64_t)));
+  CU(fn_, R.odist.ensure((size_t)yrows * 2 * sizeof(int32_t)));
+  CU(fn_, keys_finalize_i32((const unsigned long long*)R.keys.p, yrows, 2, (uint64_t*)R.oidx.p, (int32_t*)R.odist.p,
+                            R.stream));
+  CU(fn_, cudaMemcpyAsync(idx, R.oidx.p, (size_t)yrows * 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, R.stream));
+  CU(fn_, cudaMemcpyAsync(dist, R.odist.p, (size_t)yrows * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, R.stream));
+  for (int g = 0; g < G; ++g) {
+    CU(fn_, cudaSetDevice(g_rt.gpus[g].dev));
+    CU(fn_, cudaStreamSynchronize(g_rt.gpus[g].stream));
+  }
+  cudaSetDevice(prev);
+}
+
+}  // namespace spv

@@ -1,0 +1,32 @@
+// host_ctx.h -- host-side runtime behind the drop-in entry points: cached
+// per-GPU streams and device buffers, host<->device staging, and the
+// single-process multi-GPU path (train rows sharded over SPECTAVI_GPUS devices,
+// query rows broadcast, per-GPU top-2 all-gathered with NCCL and merged by K5).
+//
+// The reference keeps no state between calls (every call rebuilds everything,
+// Spectavi.cpp:326-328); the cache here holds only scratch memory and
+// communicators, never results, and is guarded by one mutex because the
+// reference's functions are re-entrant.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <mutex>
+
+namespace spv {
+
+int fail(const char* fmt, ...);
+[[noreturn]] void die(const char* fn, const char* fmt, ...);
+
+class HostCall {
+ public:
+  explicit HostCall(const char* fn);
+  ~HostCall();
+  // brute-force L1 k=2, host in / host out (reference layout: yrows x 2)
+  void l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist);
+
+ private:
+  const char* fn_;
+  std::unique_lock<std::mutex> lock_;
+};
+
+}  // namespace spv

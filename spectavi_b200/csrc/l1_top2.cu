@@ -1,0 +1,433 @@
+// l1_top2.cu -- K1: all-pairs L1 distance + per-query top-2 over uint8 rows,
+// hand-written for sm_100a.  Replaces BruteForceNnL1K2::find_neighbours
+// (reference src/BruteForceNnL1K2.h:84-145) and its SSE2 sad_16 (:43-48).
+//
+// Bound: the CUDA-core ALU pipe.  One pair of dim-byte rows costs dim/4
+// VABSDIFF4.U8.ACC (packed 4 x u8 |a-b| accumulate, 64 thread-ops/clk/SM
+// measured, pipe_peak.cu); everything else is arranged so that it does NOT
+// issue on that pipe:
+//   * operands: TMA (UTMALDG) stages 64-row train tiles and the 256-row query
+//     tile into shared memory as [16-byte k-chunk][row][16 B], so that an
+//     8 x 8 register tile per thread is fed by 16 conflict-free LDS.128 per
+//     256 VABSDIFF4 (LSU pipe, 6 % of the spare issue slots);
+//   * threshold test: each accumulator starts at -(2nd best distance of its
+//     query row), so "candidate" == "accumulator ended negative"; the 64 sign
+//     bits of a thread tile are folded with IDP.4A (fma pipe), one ISETP and
+//     one VOTE per tile;
+//   * the top-2 update itself is a rare slow path (about 2 ln(xrows) hits per
+//     query row) that keeps its (dist, idx) keys in shared memory.
+// The reference's early-exit prune (:118-121) is not reproduced: it never
+// changes the result (strict '>' there, strict '<' at :129,135), and divergent
+// early exit loses on a GPU.
+//
+// Work decomposition: units of (256 query rows) x (64 train rows); every CTA
+// owns a contiguous range of units (query-tile major), so the grid is one
+// persistent CTA per SM balanced to +-1 unit.  A CTA folds its per-thread
+// results into the global key buffer with two 64-bit atomicMin per key, so
+// train-side splits (across CTAs, launches, or GPUs) need no extra pass.
+#include "spv_common.h"
+
+#include <cuda.h>
+#include <atomic>
+#include <mutex>
+
+namespace spv {
+namespace {
+
+constexpr int BY = 256;        // query rows per CTA tile (8 warps x 32)
+constexpr int BX = 64;         // train rows per stage   (8 lanes x 8)
+constexpr int TY = 8, TX = 8;  // per-thread register tile
+constexpr int NCW = 8;         // compute warps
+constexpr int NTHREADS = (NCW + 1) * 32;  // + 1 producer warp
+constexpr int NCT = NCW * 32;
+constexpr uint32_t FULL = 0xFFFFFFFFu;
+constexpr uint32_t THR_MAX = 0x7FFFFFFFu;  // INT_MAX, BruteForceNnL1K2.h:99-103
+
+// ------------------------------------------------------------------ PTX glue
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must trap, never hang the device.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 26)) {
+      printf("l1_top2: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+// packed 4 x u8 sum of absolute differences, accumulated: SASS VABSDIFF4.U8.ACC
+__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+// s += (signed top byte of v): negative iff some folded accumulator was negative
+// (non-negative accumulators are < 2^24 for dim <= 65536).  SASS IDP.4A, fma pipe.
+__device__ __forceinline__ int fold_sign(uint32_t v, int s) {
+  int r;
+  asm("dp4a.s32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(v), "r"(0x01000000u), "r"(s));
+  return r;
+}
+
+struct Params {
+  int xrows, yrows, nk16;        // nk16 = dim / 16
+  uint32_t xoffset;              // global index of local train row 0
+  int nxt, nyt;                  // tiles along train / query
+  long long units;               // nxt * nyt
+  unsigned long long* keys;      // [2][yrows]
+};
+
+// shared memory carve-up (dynamic):  [ytile][x stages][state][barriers]
+__host__ __device__ inline size_t smem_ytile_bytes(int nk16) { return (size_t)nk16 * BY * 16; }
+__host__ __device__ inline size_t smem_xstage_bytes(int nk16) { return (size_t)nk16 * BX * 16; }
+constexpr size_t SMEM_STATE_BYTES = (size_t)2 * TY * NCT * 8;
+
+// global fold: keys[0][row] / keys[1][row] <- top2(old pair U {k}).  The loser of
+// the first atomicMin is offered to rank 1; the 2nd smallest key overall is
+// always the loser of some exchange, and no loser is smaller than it.
+__device__ __forceinline__ void fold_key(unsigned long long* keys, int yrows, int row, unsigned long long k) {
+  unsigned long long old = atomicMin(keys + row, k);
+  unsigned long long loser = old > k ? old : k;
+  if (loser != KEY_NONE) atomicMin(keys + yrows + row, loser);
+}
+
+__device__ __noinline__ void offer(unsigned long long* st, uint32_t dist, uint32_t gidx) {
+  // st[0] = best, st[TY*NCT] = second best of this (thread, row)
+  const unsigned long long key = ((unsigned long long)dist << 32) | gidx;
+  const unsigned long long k2 = st[TY * NCT];
+  if (key < k2) {
+    const unsigned long long k1 = st[0];
+    if (key < k1) { st[TY * NCT] = k1; st[0] = key; }
+    else st[TY * NCT] = key;
+  }
+}
+
+template <bool FIRST>
+__device__ __forceinline__ void kstep(uint32_t (&acc)[TY][TX], const uint32_t (&negthr)[TY], const uint4* __restrict__ ys,
+                                      const uint4* __restrict__ xs) {
+  uint4 ra[TY], rb[TX];
+#pragma unroll
+  for (int i = 0; i < TY; ++i) ra[i] = ys[i * 4];   // rows ly + 4 i
+#pragma unroll
+  for (int j = 0; j < TX; ++j) rb[j] = xs[j * 8];   // rows lx + 8 j
+#pragma unroll
+  for (int i = 0; i < TY; ++i)
+#pragma unroll
+    for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].x, rb[j].x, FIRST ? negthr[i] : acc[i][j]);
+#pragma unroll
+  for (int i = 0; i < TY; ++i)
+#pragma unroll
+    for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].y, rb[j].y, acc[i][j]);
+#pragma unroll
+  for (int i = 0; i < TY; ++i)
+#pragma unroll
+    for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].z, rb[j].z, acc[i][j]);
+#pragma unroll
+  for (int i = 0; i < TY; ++i)
+#pragma unroll
+    for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].w, rb[j].w, acc[i][j]);
+}
+
+template <int NST>
+__global__ void __launch_bounds__(NTHREADS, 1)
+l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmy, const Params p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int nk16 = p.nk16;
+  unsigned char* ytile = smem;
+  unsigned char* xst = ytile + smem_ytile_bytes(nk16);
+  unsigned long long* state = reinterpret_cast<unsigned long long*>(xst + NST * smem_xstage_bytes(nk16));
+  unsigned long long* bars = state + 2 * TY * NCT;
+  // bars: full[NST], empty[NST], yfull, yempty
+  const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NST;
+  const uint32_t bar_yfull = bar_empty + 8 * NST, bar_yempty = bar_yfull + 8;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NST; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, NCW); }
+    mbar_init(bar_yfull, 1);
+    mbar_init(bar_yempty, NCW);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // contiguous unit range of this CTA
+  const long long u0 = p.units * blockIdx.x / gridDim.x;
+  const long long u1 = p.units * (blockIdx.x + 1) / gridDim.x;
+  if (u0 >= u1) return;
+  int yt = (int)(u0 / p.nxt), xt = (int)(u0 % p.nxt);
+
+  if (warp == NCW) {
+    // ===================== producer: one thread issues all TMA loads
+    if (lane == 0) {
+      const uint32_t ytile_s = smem_u32(ytile), xst_s = smem_u32(xst);
+      const uint32_t xbytes = (uint32_t)smem_xstage_bytes(nk16), ybytes = (uint32_t)smem_ytile_bytes(nk16);
+      int stage = 0;
+      uint32_t phase = 0, yphase = 0;
+      bool newy = true, firsty = true;
+      for (long long u = u0; u < u1; ++u) {
+        if (newy) {
+          if (!firsty) { mbar_wait(bar_yempty, yphase); yphase ^= 1; }
+          firsty = false;
+          mbar_expect_tx(bar_yfull, ybytes);
+          for (int c = 0; c < nk16; ++c) tma_load_2d(ytile_s + c * (BY * 16), &tmy, c * 16, yt * BY, bar_yfull);
+          newy = false;
+        }
+        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+        mbar_expect_tx(bar_full + 8 * stage, xbytes);
+        const uint32_t dst = xst_s + stage * xbytes;
+        for (int c = 0; c < nk16; ++c) tma_load_2d(dst + c * (BX * 16), &tmx, c * 16, xt * BX, bar_full + 8 * stage);
+        if (++stage == NST) { stage = 0; phase ^= 1; }
+        if (++xt == p.nxt) { xt = 0; ++yt; newy = true; }
+      }
+    }
+    return;
+  }
+
+  // ===================== compute warps
+  const int ly = lane >> 3, lx = lane & 7;
+  const int ctid = threadIdx.x;                                   // 0..255
+  unsigned long long* st = state + ctid;                          // + (slot*TY + i) * NCT
+  const uint4* ys = reinterpret_cast<const uint4*>(ytile) + warp * 32 + ly;   // + c*BY + 4 i
+  const uint4* xs0 = reinterpret_cast<const uint4*>(xst) + lx;                // + stage*nk16*BX + c*BX + 8 j
+  const int xstage_u4 = nk16 * BX;
+
+  uint32_t acc[TY][TX];
+  uint32_t negthr[TY];
+  int stage = 0;
+  uint32_t phase = 0, yphase = 0;
+  int cur_yt = -1;
+
+  auto flush = [&](int ytile_idx) {
+#pragma unroll
+    for (int i = 0; i < TY; ++i) {
+      const int row = ytile_idx * BY + warp * 32 + ly + 4 * i;
+      if (row < p.yrows) {
+        const unsigned long long k1 = st[i * NCT], k2 = st[(TY + i) * NCT];
+        if (k1 != KEY_NONE) fold_key(p.keys, p.yrows, row, k1);
+        if (k2 != KEY_NONE) fold_key(p.keys, p.yrows, row, k2);
+      }
+    }
+  };
+
+  for (long long u = u0; u < u1; ++u) {
+    if (yt != cur_yt) {
+      if (cur_yt >= 0) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_yempty);   // this warp no longer reads the old query tile
+        flush(cur_yt);
+      }
+#pragma unroll
+      for (int i = 0; i < TY; ++i) { st[i * NCT] = KEY_NONE; st[(TY + i) * NCT] = KEY_NONE; negthr[i] = 0u - THR_MAX; }
+      mbar_wait(bar_yfull, yphase);
+      yphase ^= 1;
+      cur_yt = yt;
+    }
+    mbar_wait(bar_full + 8 * stage, phase);
+    const uint4* xs = xs0 + stage * xstage_u4;
+    kstep<true>(acc, negthr, ys, xs);
+#pragma unroll 1
+    for (int c = 1; c < nk16; ++c) kstep<false>(acc, negthr, ys + c * BY, xs + c * BX);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_empty + 8 * stage);   // operands are in registers: release the stage
+
+    // candidate test: any accumulator negative  <=>  some dist < 2nd best of its row
+    int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma unroll
+    for (int i = 0; i < TY; ++i)
+#pragma unroll
+      for (int j = 0; j < TX; j += 4) {
+        s0 = fold_sign(acc[i][j], s0); s1 = fold_sign(acc[i][j + 1], s1);
+        s2 = fold_sign(acc[i][j + 2], s2); s3 = fold_sign(acc[i][j + 3], s3);
+      }
+    if (__any_sync(FULL, (s0 + s1 + s2 + s3) < 0)) {
+      // slow path (rare): exact (dist, idx) insertion, then tighten the row thresholds
+      const uint32_t g0 = (uint32_t)(xt * BX + lx);
+#pragma unroll
+      for (int i = 0; i < TY; ++i) {
+        const uint32_t thr = 0u - negthr[i];
+#pragma unroll
+        for (int j = 0; j < TX; ++j) {
+          const uint32_t lidx = g0 + 8 * j;
+          if ((int)acc[i][j] < 0 && lidx < (uint32_t)p.xrows) offer(st + i * NCT, acc[i][j] + thr, p.xoffset + lidx);
+        }
+        // every train index seen later is larger than any stored one, so a later
+        // candidate must beat the row's 2nd best distance STRICTLY: share the
+        // tightest 2nd-best among the 8 lanes that split this row's train columns
+        uint32_t d2 = (uint32_t)(st[(TY + i) * NCT] >> 32);
+        d2 = min(d2, THR_MAX);
+        d2 = min(d2, __shfl_xor_sync(FULL, d2, 1));
+        d2 = min(d2, __shfl_xor_sync(FULL, d2, 2));
+        d2 = min(d2, __shfl_xor_sync(FULL, d2, 4));
+        negthr[i] = 0u - d2;
+      }
+    }
+    if (++stage == NST) { stage = 0; phase ^= 1; }
+    if (++xt == p.nxt) { xt = 0; ++yt; }
+  }
+  flush(cur_yt);
+}
+
+// ------------------------------------------------------- small helper kernels
+__global__ void keys_merge_kernel(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src,
+                                  int nsrc, int yrows) {
+  // K5: lexicographic top-2 of dst's pair and nsrc more pairs per query row
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= yrows) return;
+  unsigned long long a = dst[row], b = dst[yrows + row];
+  for (int s = 0; s < nsrc; ++s) {
+    const unsigned long long* q = src + (size_t)s * 2 * yrows;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const unsigned long long k = q[(size_t)r * yrows + row];
+      if (k < a) { b = a; a = k; }
+      else if (k < b && k != a) b = k;   // k == a: the same train row offered twice
+    }
+  }
+  dst[row] = a;
+  dst[yrows + row] = b;
+}
+
+template <typename D>
+__global__ void keys_finalize_kernel(const unsigned long long* __restrict__ keys, int yrows, int kcols,
+                                     uint64_t* __restrict__ idx, D* __restrict__ dist) {
+  // BruteForceNnL1K2.h:99-103 sentinels: idx (size_t)-1, dist INT_MAX; the cascade
+  // reports (float)INT_MAX (CascadingHashNn.h:244).  Columns >= 2 (k > 2 on the
+  // cascade ABI, Spectavi.cpp:329-334) are left as the caller's zeros.
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= yrows) return;
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    if (r >= kcols) break;
+    const unsigned long long k = keys[(size_t)r * yrows + row];
+    const bool none = (k == KEY_NONE);
+    idx[(size_t)row * kcols + r] = none ? ~0ull : (k & 0xFFFFFFFFull);
+    dist[(size_t)row * kcols + r] = none ? (D)2147483647 : (D)(int32_t)(k >> 32);
+  }
+}
+
+// -------------------------------------------------------------- host helpers
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// rows x dim uint8, row-major; box = 16 bytes x box_rows rows (one k-chunk of a tile)
+bool make_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)dim};
+  cuuint32_t box[2] = {16u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(base), gdim, gstride, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+std::atomic<unsigned long long> g_launches{0};
+
+template <int NST>
+cudaError_t launch_tiled(const CUtensorMap& tmx, const CUtensorMap& tmy, const Params& p, int sms, cudaStream_t stream) {
+  const size_t smem = smem_ytile_bytes(p.nk16) + NST * smem_xstage_bytes(p.nk16) + SMEM_STATE_BYTES + (2 * NST + 2) * 8;
+  cudaError_t e = cudaFuncSetAttribute(l1_top2_kernel<NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int grid = (int)(p.units < sms ? p.units : sms);
+  l1_top2_kernel<NST><<<grid, NTHREADS, smem, stream>>>(tmx, tmy, p);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+unsigned long long launches() { return g_launches.load(); }
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n); }
+
+cudaError_t keys_reset(unsigned long long* keys, int yrows, cudaStream_t stream) {
+  if (yrows <= 0) return cudaSuccess;
+  return cudaMemsetAsync(keys, 0xFF, (size_t)2 * yrows * sizeof(unsigned long long), stream);
+}
+
+cudaError_t keys_merge(unsigned long long* dst, const unsigned long long* src, int nsrc, int yrows, cudaStream_t stream) {
+  if (yrows <= 0 || nsrc <= 0) return cudaSuccess;
+  keys_merge_kernel<<<(yrows + 255) / 256, 256, 0, stream>>>(dst, src, nsrc, yrows);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t keys_finalize_i32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx, int32_t* dist,
+                              cudaStream_t stream) {
+  if (yrows <= 0) return cudaSuccess;
+  keys_finalize_kernel<int32_t><<<(yrows + 255) / 256, 256, 0, stream>>>(keys, yrows, kcols, idx, dist);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx, float* dist,
+                              cudaStream_t stream) {
+  if (yrows <= 0) return cudaSuccess;
+  keys_finalize_kernel<float><<<(yrows + 255) / 256, 256, 0, stream>>>(keys, yrows, kcols, idx, dist);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t l1_top2_u8(const uint8_t* dx, const uint8_t* dy, int xrows, int yrows, int dim, uint32_t xoffset,
+                       unsigned long long* keys, cudaStream_t stream) {
+  if (xrows <= 0 || yrows <= 0) return cudaSuccess;   // nothing to fold in
+  if (dim <= 0 || dim % 16 != 0 || dim > 512) return cudaErrorInvalidValue;
+  int dev = 0, sms = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return e;
+  CUtensorMap tmx, tmy;
+  if (!make_map(&tmx, dx, xrows, dim, BX) || !make_map(&tmy, dy, yrows, dim, BY)) return cudaErrorInvalidValue;
+  Params p;
+  p.xrows = xrows; p.yrows = yrows; p.nk16 = dim / 16; p.xoffset = xoffset;
+  p.nxt = (xrows + BX - 1) / BX; p.nyt = (yrows + BY - 1) / BY;
+  p.units = (long long)p.nxt * p.nyt;
+  p.keys = keys;
+  if (dim <= 256) return launch_tiled<4>(tmx, tmy, p, sms, stream);
+  return launch_tiled<2>(tmx, tmy, p, sms, stream);
+}
+
+}  // namespace spv

@@ -11,6 +11,7 @@
 // An "op" is one thread-level instruction of the kind under test; for the SAD
 // formulations the table also gives byte-lanes per clk per SM.
 #include <cuda_runtime.h>
+#include "../../include/spectavi_b200.h"
 #include <cuda_fp16.h>
 #include <cstdint>
 #include <cstdio>

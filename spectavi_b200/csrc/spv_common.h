@@ -1,0 +1,45 @@
+// spv_common.h -- shared declarations of the device-side matcher (internal).
+//
+// Result representation used by every kernel of the path: one 64-bit KEY per
+// (query row, rank):   key = (uint64)dist << 32 | global_train_index.
+// Unsigned comparison of keys IS the reference's selection rule: the scan of
+// src/BruteForceNnL1K2.h:109-142 walks x ascending and updates on strict '<',
+// so its answer is the two lexicographically smallest (dist, idx) pairs.  Any
+// tiling, any merge order and any number of GPUs therefore give the same bits.
+// "no neighbour" (BruteForceNnL1K2.h:99-103: dist INT_MAX, idx (size_t)-1) is
+// the all-ones key, which loses every comparison.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+
+namespace spv {
+
+constexpr unsigned long long KEY_NONE = 0xFFFFFFFFFFFFFFFFull;
+
+// keys layout on device: keys[rank * yrows + yrow], rank in {0,1}
+struct KeyBuf {
+  unsigned long long* keys;
+  int yrows;
+};
+
+// ---- l1_top2.cu : K1, brute-force L1 k=2 over uint8 rows -------------------
+// Accumulates the top-2 of y against x[0..xrows) (global index = xoffset + row)
+// INTO keys (which must have been reset or hold earlier partial results).
+cudaError_t l1_top2_u8(const uint8_t* dx, const uint8_t* dy, int xrows, int yrows, int dim,
+                       uint32_t xoffset, unsigned long long* keys, cudaStream_t stream);
+cudaError_t keys_reset(unsigned long long* keys, int yrows, cudaStream_t stream);
+// K5: keys_dst = top2(keys_dst U src[0] U ... U src[nsrc-1]); src s at src + s*2*yrows
+cudaError_t keys_merge(unsigned long long* dst, const unsigned long long* src, int nsrc, int yrows,
+                       cudaStream_t stream);
+// keys -> reference output arrays (row-major yrows x 2): size_t idx, int32 dist
+cudaError_t keys_finalize_i32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx,
+                              int32_t* dist, cudaStream_t stream);
+// same but distances as float (CascadingHashNn.h:244 casts int -> float)
+cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx,
+                              float* dist, cudaStream_t stream);
+// launch count bookkeeping (bench.py's gpu_launches)
+unsigned long long launches();
+void count_launch(int n = 1);
+
+}  // namespace spv

@@ -1,0 +1,130 @@
+"""Host-side mirror of the reference's NN wrappers (spectavi/feature.py:202-304,
+340-407): same names, argument meaning, dtypes and return shapes; the ctypes
+prototypes are the reference's own (feature.py:208-243,346-358), bound to the
+B200 ``libspectavi.so``.  Everything below the ctypes call runs on the GPU;
+this module adds no CPU compute beyond what the reference's wrappers do in
+numpy themselves (``use_int`` rounding, the auto-``m`` rule, the quantiser).
+"""
+import ctypes as ct
+
+import numpy as np
+from numpy.ctypeslib import ndpointer
+
+from ._libspectavi import clib
+from .cndarray import NdArray
+
+_nn_bruteforce = clib.nn_bruteforce
+_nn_bruteforce.restype = None
+_nn_bruteforce.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                           ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                           ct.c_int, ct.c_int, ct.c_int, ct.c_int,
+                           ct.c_float, ct.c_float,
+                           ct.POINTER(NdArray), ct.POINTER(NdArray)]
+
+_nn_bruteforcei = clib.nn_bruteforcei
+_nn_bruteforcei.restype = None
+_nn_bruteforcei.argtypes = [ndpointer(ct.c_int, flags="C_CONTIGUOUS"),
+                            ndpointer(ct.c_int, flags="C_CONTIGUOUS"),
+                            ct.c_int, ct.c_int, ct.c_int, ct.c_int,
+                            ct.c_float, ct.c_float,
+                            ct.POINTER(NdArray), ct.POINTER(NdArray)]
+
+_nn_bruteforcel1k2 = clib.nn_bruteforcel1k2
+_nn_bruteforcel1k2.restype = None
+_nn_bruteforcel1k2.argtypes = [ndpointer(ct.c_ubyte, flags="C_CONTIGUOUS"),
+                               ndpointer(ct.c_ubyte, flags="C_CONTIGUOUS"),
+                               ct.c_int, ct.c_int, ct.c_int, ct.c_int,
+                               ct.POINTER(NdArray), ct.POINTER(NdArray)]
+
+_nn_cascading_hash = clib.nn_cascading_hash
+_nn_cascading_hash.restype = None
+_nn_cascading_hash.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                               ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                               ct.c_int, ct.c_int, ct.c_int, ct.c_int,
+                               ct.c_int, ct.c_int, ct.c_int,
+                               ct.POINTER(NdArray), ct.POINTER(NdArray)]
+
+
+def nn_bruteforce(x, y, p=.5, mu=0., k=2, use_int=False):
+    """k nearest rows of ``x`` for every row of ``y`` under sum |d|^p
+    (reference feature.py:246-289).  Returns ``(idx uint64, dist)`` of shape
+    ``(yrows, k)``, ascending; ``dist`` is float32, or int32 with ``use_int``
+    (inputs rounded to ``round(100 * v)`` as the reference does, :286-287)."""
+    xrows, xdim = x.shape
+    yrows, ydim = y.shape
+    assert ydim == xdim
+    dim = xdim
+    nn_idx = NdArray(dtype='uint64')
+    if not use_int:
+        nn_dist = NdArray(dtype='float32')
+        _nn_bruteforce(x, y, xrows, yrows, dim, k, p, mu, nn_idx, nn_dist)
+    else:
+        nn_dist = NdArray(dtype='int32')
+        xi = np.round(100 * x).astype('int32')
+        yi = np.round(100 * y).astype('int32')
+        _nn_bruteforcei(xi, yi, xrows, yrows, dim, k, p, mu, nn_idx, nn_dist)
+    return nn_idx.asarray(), nn_dist.asarray()
+
+
+def nn_bruteforcel1k2(x, y, nthreads=1):
+    """Exact L1 2-nearest-neighbour of every ``y`` row among ``x`` rows; uint8
+    inputs, ``dim % 16 == 0`` (reference feature.py:292-304).  ``nthreads`` is
+    kept for call compatibility and ignored (the work runs on the GPU)."""
+    xrows, xdim = x.shape
+    yrows, ydim = y.shape
+    assert ydim == xdim
+    dim = xdim
+    nn_idx = NdArray(dtype='uint64')
+    nn_dist = NdArray(dtype='int32')
+    _nn_bruteforcel1k2(x, y, xrows, yrows, dim, nthreads, nn_idx, nn_dist)
+    return nn_idx.asarray(), nn_dist.asarray()
+
+
+def nn_cascading_hash(x, y, k=2, m=None, n=2, g=2):
+    """Cascade-of-hashes matcher (reference feature.py:360-376): ``n`` tables of
+    ``m``-bit random-hyperplane codes, multi-probe on the ``g`` least confident
+    bits, exact L1 k=2 re-rank of the candidates.  ``m=None`` applies the
+    reference's ~6-rows-per-bucket rule and falls back to brute force (int32
+    distances, as the reference) when that gives fewer than 4 bits."""
+    xrows, xdim = x.shape
+    yrows, ydim = y.shape
+    assert ydim == xdim
+    if m is None:
+        mrows = max([xrows, yrows])
+        m = int(np.floor(np.log2(mrows / 6.)))
+        if m < 4:
+            return nn_bruteforcel1k2((x + 128).astype('uint8'),
+                                     (y + 128).astype('uint8'), nthreads=8)
+    dim = xdim
+    cashash_idx = NdArray(dtype='uint64')
+    cashash_dist = NdArray(dtype='float32')
+    _nn_cascading_hash(x, y, xrows, yrows, dim, k, m, n, g, cashash_idx,
+                       cashash_dist)
+    return cashash_idx.asarray(), cashash_dist.asarray()
+
+
+def normalize_to_ubyte_and_multiple_16_dim(x, dtype='float32'):
+    """Column de-mean, scale to [-128, 127], round half-to-even, zero-pad the
+    columns to a multiple of 16 (reference feature.py:384-407; host numpy in
+    the reference too -- a constant column yields NaN there and here)."""
+    x0 = x - np.mean(x, axis=0, keepdims=True)
+    hi = np.max(x0, axis=0, keepdims=True)
+    lo = np.min(x0, axis=0, keepdims=True)
+    norm = np.max(np.stack([hi, -lo]), axis=0)
+    x0 = np.round(x0 / norm * 128)
+    x0[x0 > 127] = 127
+    x0[x0 < -128] = -128
+    xrows, dim = x0.shape
+    new_dim = int(np.ceil(dim / 16.) * 16)
+    xx = np.zeros([xrows, new_dim])
+    xx[:, :dim] = x0
+    return xx.astype(dtype)
+
+
+def ratio_test(nn_dist, min_ratio=1.75):
+    """The example's ratio test (example/ex01_essential_estimation.py:102-103):
+    ``second / first >= min_ratio`` in float64; x/0 -> inf passes, 0/0 -> nan
+    fails."""
+    with np.errstate(divide='ignore', invalid='ignore'):
+        ratio = nn_dist[:, 1] / nn_dist[:, 0].astype('float64')
+    return ratio >= min_ratio
