@@ -15,7 +15,8 @@
 //     bits of a thread tile are folded with IDP.4A (fma pipe), one ISETP and
 //     one VOTE per tile;
 //   * the top-2 update itself is a rare slow path (about 2 ln(xrows) hits per
-//     query row) that keeps its (dist, idx) keys in shared memory.
+//     query row) that keeps one (best, second) key pair per query row in shared
+//     memory, updated with 64-bit atomicMin.
 // The reference's early-exit prune (:118-121) is not reproduced: it never
 // changes the result (strict '>' there, strict '<' at :129,135), and divergent
 // early exit loses on a GPU.
@@ -39,7 +40,6 @@ constexpr int BX = 64;         // train rows per stage   (8 lanes x 8)
 constexpr int TY = 8, TX = 8;  // per-thread register tile
 constexpr int NCW = 8;         // compute warps
 constexpr int NTHREADS = (NCW + 1) * 32;  // + 1 producer warp
-constexpr int NCT = NCW * 32;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 constexpr uint32_t THR_MAX = 0x7FFFFFFFu;  // INT_MAX, BruteForceNnL1K2.h:99-103
 
@@ -77,6 +77,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
   }
 }
+// Producer-side wait: the slot it waits for is microseconds away; back off
+// between polls so the spin does not take issue / ALU slots from the two
+// compute warps that share its scheduler.
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(128);
+    if (++spins > (1u << 24)) {
+      printf("l1_top2: producer mbarrier wait timed out (block %d)\n", blockIdx.x);
+      __trap();
+    }
+  }
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
@@ -108,7 +121,7 @@ struct Params {
 // shared memory carve-up (dynamic):  [ytile][x stages][state][barriers]
 __host__ __device__ inline size_t smem_ytile_bytes(int nk16) { return (size_t)nk16 * BY * 16; }
 __host__ __device__ inline size_t smem_xstage_bytes(int nk16) { return (size_t)nk16 * BX * 16; }
-constexpr size_t SMEM_STATE_BYTES = (size_t)2 * TY * NCT * 8;
+constexpr size_t SMEM_STATE_BYTES = (size_t)2 * BY * 8;   // best[BY], second[BY] keys of the CTA's query tile
 
 // global fold: keys[0][row] / keys[1][row] <- top2(old pair U {k}).  The loser of
 // the first atomicMin is offered to rank 1; the 2nd smallest key overall is
@@ -119,15 +132,15 @@ __device__ __forceinline__ void fold_key(unsigned long long* keys, int yrows, in
   if (loser != KEY_NONE) atomicMin(keys + yrows + row, loser);
 }
 
-__device__ __noinline__ void offer(unsigned long long* st, uint32_t dist, uint32_t gidx) {
-  // st[0] = best, st[TY*NCT] = second best of this (thread, row)
+// slow path: offer one candidate to its query row's (best, second) keys in shared
+// memory.  The 8 lanes that split a row's train columns share ONE pair per row, so
+// the row threshold is the true running 2nd-best (a per-lane pair would make it
+// about the 10th-best and the slow path 4x more frequent: ncu r01, 39 % of tiles).
+__device__ __noinline__ void offer(unsigned long long* best, uint32_t dist, uint32_t gidx) {
   const unsigned long long key = ((unsigned long long)dist << 32) | gidx;
-  const unsigned long long k2 = st[TY * NCT];
-  if (key < k2) {
-    const unsigned long long k1 = st[0];
-    if (key < k1) { st[TY * NCT] = k1; st[0] = key; }
-    else st[TY * NCT] = key;
-  }
+  const unsigned long long old = atomicMin(best, key);
+  const unsigned long long loser = old > key ? old : key;
+  if (loser != KEY_NONE) atomicMin(best + BY, loser);
 }
 
 template <bool FIRST>
@@ -164,7 +177,7 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
   unsigned char* ytile = smem;
   unsigned char* xst = ytile + smem_ytile_bytes(nk16);
   unsigned long long* state = reinterpret_cast<unsigned long long*>(xst + NST * smem_xstage_bytes(nk16));
-  unsigned long long* bars = state + 2 * TY * NCT;
+  unsigned long long* bars = state + 2 * BY;
   // bars: full[NST], empty[NST], yfull, yempty
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NST;
   const uint32_t bar_yfull = bar_empty + 8 * NST, bar_yempty = bar_yfull + 8;
@@ -194,13 +207,13 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
       bool newy = true, firsty = true;
       for (long long u = u0; u < u1; ++u) {
         if (newy) {
-          if (!firsty) { mbar_wait(bar_yempty, yphase); yphase ^= 1; }
+          if (!firsty) { mbar_wait_sleep(bar_yempty, yphase); yphase ^= 1; }
           firsty = false;
           mbar_expect_tx(bar_yfull, ybytes);
           for (int c = 0; c < nk16; ++c) tma_load_2d(ytile_s + c * (BY * 16), &tmy, c * 16, yt * BY, bar_yfull);
           newy = false;
         }
-        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+        mbar_wait_sleep(bar_empty + 8 * stage, phase ^ 1);
         mbar_expect_tx(bar_full + 8 * stage, xbytes);
         const uint32_t dst = xst_s + stage * xbytes;
         for (int c = 0; c < nk16; ++c) tma_load_2d(dst + c * (BX * 16), &tmx, c * 16, xt * BX, bar_full + 8 * stage);
@@ -213,8 +226,7 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
 
   // ===================== compute warps
   const int ly = lane >> 3, lx = lane & 7;
-  const int ctid = threadIdx.x;                                   // 0..255
-  unsigned long long* st = state + ctid;                          // + (slot*TY + i) * NCT
+  unsigned long long* st = state + warp * 32;                     // this warp's 32 rows: best at [r], second at [BY + r]
   const uint4* ys = reinterpret_cast<const uint4*>(ytile) + warp * 32 + ly;   // + c*BY + 4 i
   const uint4* xs0 = reinterpret_cast<const uint4*>(xst) + lx;                // + stage*nk16*BX + c*BX + 8 j
   const int xstage_u4 = nk16 * BX;
@@ -225,16 +237,15 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
   uint32_t phase = 0, yphase = 0;
   int cur_yt = -1;
 
-  auto flush = [&](int ytile_idx) {
-#pragma unroll
-    for (int i = 0; i < TY; ++i) {
-      const int row = ytile_idx * BY + warp * 32 + ly + 4 * i;
-      if (row < p.yrows) {
-        const unsigned long long k1 = st[i * NCT], k2 = st[(TY + i) * NCT];
-        if (k1 != KEY_NONE) fold_key(p.keys, p.yrows, row, k1);
-        if (k2 != KEY_NONE) fold_key(p.keys, p.yrows, row, k2);
-      }
+  auto flush = [&](int ytile_idx) {   // lane r publishes row warp*32 + r
+    __syncwarp();
+    const int row = ytile_idx * BY + warp * 32 + lane;
+    if (row < p.yrows) {
+      const unsigned long long k1 = st[lane], k2 = st[BY + lane];
+      if (k1 != KEY_NONE) fold_key(p.keys, p.yrows, row, k1);
+      if (k2 != KEY_NONE) fold_key(p.keys, p.yrows, row, k2);
     }
+    __syncwarp();
   };
 
   for (long long u = u0; u < u1; ++u) {
@@ -244,8 +255,11 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
         if (lane == 0) mbar_arrive(bar_yempty);   // this warp no longer reads the old query tile
         flush(cur_yt);
       }
+      st[lane] = KEY_NONE;
+      st[BY + lane] = KEY_NONE;
+      __syncwarp();
 #pragma unroll
-      for (int i = 0; i < TY; ++i) { st[i * NCT] = KEY_NONE; st[(TY + i) * NCT] = KEY_NONE; negthr[i] = 0u - THR_MAX; }
+      for (int i = 0; i < TY; ++i) negthr[i] = 0u - THR_MAX;
       mbar_wait(bar_yfull, yphase);
       yphase ^= 1;
       cur_yt = yt;
@@ -276,17 +290,16 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
 #pragma unroll
         for (int j = 0; j < TX; ++j) {
           const uint32_t lidx = g0 + 8 * j;
-          if ((int)acc[i][j] < 0 && lidx < (uint32_t)p.xrows) offer(st + i * NCT, acc[i][j] + thr, p.xoffset + lidx);
+          if ((int)acc[i][j] < 0 && lidx < (uint32_t)p.xrows) offer(st + ly + 4 * i, acc[i][j] + thr, p.xoffset + lidx);
         }
-        // every train index seen later is larger than any stored one, so a later
-        // candidate must beat the row's 2nd best distance STRICTLY: share the
-        // tightest 2nd-best among the 8 lanes that split this row's train columns
-        uint32_t d2 = (uint32_t)(st[(TY + i) * NCT] >> 32);
-        d2 = min(d2, THR_MAX);
-        d2 = min(d2, __shfl_xor_sync(FULL, d2, 1));
-        d2 = min(d2, __shfl_xor_sync(FULL, d2, 2));
-        d2 = min(d2, __shfl_xor_sync(FULL, d2, 4));
-        negthr[i] = 0u - d2;
+      }
+      __syncwarp();
+      // every train index seen later is larger than any stored one, so a later
+      // candidate must beat the row's running 2nd-best distance STRICTLY
+#pragma unroll
+      for (int i = 0; i < TY; ++i) {
+        const uint32_t d2 = (uint32_t)(st[BY + ly + 4 * i] >> 32);
+        negthr[i] = 0u - min(d2, THR_MAX);
       }
     }
     if (++stage == NST) { stage = 0; phase ^= 1; }
