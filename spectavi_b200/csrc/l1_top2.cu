@@ -90,10 +90,13 @@ __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
     }
   }
 }
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+// whole tile in one op: the tensor map (make_map) views the row-major matrix as
+// (16 B, rows, dim/16 chunks) with strides (1, dim, 16), so a box of
+// (16, box_rows, dim/16) lands in shared memory as [chunk][row][16 B]
+__device__ __forceinline__ void tma_load_tile(uint32_t dst, const CUtensorMap* map, int row0, uint32_t bar) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst), "l"(map), "r"(0), "r"(row0), "r"(0), "r"(bar)
       : "memory");
 }
 // packed 4 x u8 sum of absolute differences, accumulated: SASS VABSDIFF4.U8.ACC
@@ -116,6 +119,7 @@ struct Params {
   int nxt, nyt;                  // tiles along train / query
   long long units;               // nxt * nyt
   unsigned long long* keys;      // [2][yrows]
+  int nst;                       // train-tile stages in the shared-memory ring
 };
 
 // shared memory carve-up (dynamic):  [ytile][x stages][state][barriers]
@@ -169,11 +173,10 @@ __device__ __forceinline__ void kstep(uint32_t (&acc)[TY][TX], const uint32_t (&
     for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].w, rb[j].w, acc[i][j]);
 }
 
-template <int NST>
 __global__ void __launch_bounds__(NTHREADS, 1)
 l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmy, const Params p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const int nk16 = p.nk16;
+  const int nk16 = p.nk16, NST = p.nst;
   unsigned char* ytile = smem;
   unsigned char* xst = ytile + smem_ytile_bytes(nk16);
   unsigned long long* state = reinterpret_cast<unsigned long long*>(xst + NST * smem_xstage_bytes(nk16));
@@ -210,13 +213,12 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
           if (!firsty) { mbar_wait_sleep(bar_yempty, yphase); yphase ^= 1; }
           firsty = false;
           mbar_expect_tx(bar_yfull, ybytes);
-          for (int c = 0; c < nk16; ++c) tma_load_2d(ytile_s + c * (BY * 16), &tmy, c * 16, yt * BY, bar_yfull);
+          tma_load_tile(ytile_s, &tmy, yt * BY, bar_yfull);
           newy = false;
         }
         mbar_wait_sleep(bar_empty + 8 * stage, phase ^ 1);
         mbar_expect_tx(bar_full + 8 * stage, xbytes);
-        const uint32_t dst = xst_s + stage * xbytes;
-        for (int c = 0; c < nk16; ++c) tma_load_2d(dst + c * (BX * 16), &tmx, c * 16, xt * BX, bar_full + 8 * stage);
+        tma_load_tile(xst_s + stage * xbytes, &tmx, xt * BX, bar_full + 8 * stage);
         if (++stage == NST) { stage = 0; phase ^= 1; }
         if (++xt == p.nxt) { xt = 0; ++yt; newy = true; }
       }
@@ -347,6 +349,7 @@ __global__ void keys_finalize_kernel(const unsigned long long* __restrict__ keys
 }
 
 // -------------------------------------------------------------- host helpers
+std::atomic<unsigned long long> g_launches{0};
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -364,28 +367,36 @@ EncodeTiledFn encode_tiled() {
   return fn;
 }
 
-// rows x dim uint8, row-major; box = 16 bytes x box_rows rows (one k-chunk of a tile)
+// rows x dim uint8, row-major, seen as 3-D (16 B, rows, dim/16) with byte strides
+// (1, dim, 16); box = (16, box_rows, dim/16) = one whole tile, delivered to shared
+// memory k-chunk-major.  Measured (tools/ubench_tma_box.cu): one such op fills an
+// 8 KB stage in 544 cycles with 148 SMs streaming, vs 850 as 8 separate 16 B boxes.
 bool make_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows) {
   EncodeTiledFn enc = encode_tiled();
   if (!enc) return false;
-  cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
-  cuuint64_t gstride[1] = {(cuuint64_t)dim};
-  cuuint32_t box[2] = {16u, (cuuint32_t)box_rows};
-  cuuint32_t estr[2] = {1u, 1u};
-  return enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(base), gdim, gstride, box, estr,
+  cuuint64_t gdim[3] = {16u, (cuuint64_t)rows, (cuuint64_t)(dim / 16)};
+  cuuint64_t gstride[2] = {(cuuint64_t)dim, 16u};
+  cuuint32_t box[3] = {16u, (cuuint32_t)box_rows, (cuuint32_t)(dim / 16)};
+  cuuint32_t estr[3] = {1u, 1u, 1u};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), gdim, gstride, box, estr,
              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-std::atomic<unsigned long long> g_launches{0};
-
-template <int NST>
-cudaError_t launch_tiled(const CUtensorMap& tmx, const CUtensorMap& tmy, const Params& p, int sms, cudaStream_t stream) {
-  const size_t smem = smem_ytile_bytes(p.nk16) + NST * smem_xstage_bytes(p.nk16) + SMEM_STATE_BYTES + (2 * NST + 2) * 8;
-  cudaError_t e = cudaFuncSetAttribute(l1_top2_kernel<NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+cudaError_t launch_tiled(const CUtensorMap& tmx, const CUtensorMap& tmy, Params p, int sms, cudaStream_t stream) {
+  // as many ring stages as fit beside the query tile: the ring is also the slack
+  // between the 8 compute warps (a warp may run at most nst tiles ahead of the
+  // slowest one), and slow-path hits make their pace uneven
+  const size_t fixed = smem_ytile_bytes(p.nk16) + SMEM_STATE_BYTES + 1024, budget = 200 * 1024;
+  int nst = (int)((budget - fixed) / smem_xstage_bytes(p.nk16));
+  nst = nst > 16 ? 16 : nst;
+  if (nst < 2) return cudaErrorInvalidValue;
+  p.nst = nst;
+  const size_t smem = smem_ytile_bytes(p.nk16) + nst * smem_xstage_bytes(p.nk16) + SMEM_STATE_BYTES + (2 * nst + 2) * 8;
+  cudaError_t e = cudaFuncSetAttribute(l1_top2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per device
   if (e != cudaSuccess) return e;
   const int grid = (int)(p.units < sms ? p.units : sms);
-  l1_top2_kernel<NST><<<grid, NTHREADS, smem, stream>>>(tmx, tmy, p);
+  l1_top2_kernel<<<grid, NTHREADS, smem, stream>>>(tmx, tmy, p);
   count_launch();
   return cudaGetLastError();
 }
@@ -439,8 +450,7 @@ cudaError_t l1_top2_u8(const uint8_t* dx, const uint8_t* dy, int xrows, int yrow
   p.nxt = (xrows + BX - 1) / BX; p.nyt = (yrows + BY - 1) / BY;
   p.units = (long long)p.nxt * p.nyt;
   p.keys = keys;
-  if (dim <= 256) return launch_tiled<4>(tmx, tmy, p, sms, stream);
-  return launch_tiled<2>(tmx, tmy, p, sms, stream);
+  return launch_tiled(tmx, tmy, p, sms, stream);
 }
 
 }  // namespace spv
