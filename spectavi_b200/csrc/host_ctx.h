@@ -23,6 +23,9 @@ class HostCall {
   ~HostCall();
   // brute-force L1 k=2, host in / host out (reference layout: yrows x 2)
   void l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist);
+  // brute-force sum |x-y|^p top-k over float32 / int32 rows (yrows x k out)
+  void lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p, uint64_t* idx,
+           void* dist);
 
  private:
   const char* fn_;

