@@ -1,0 +1,671 @@
+// cascade.cu -- the cascade-of-hashes matcher on sm_100a: replaces CascadingHashNn
+// (reference src/CascadingHashNn.h) behind nn_cascading_hash (Spectavi.cpp:321-336).
+//
+//   K0 f32_to_u8          x.cast<uint8>() += 128            (CascadingHashNn.h:236-239)
+//   K2 hash_project_kernel R = D * H on the tensor cores (tcgen05.mma, accumulators
+//                         in TMEM), sign-packed to one int32 code per (row, table)
+//                         (:102-135); for query rows also the g least-confident
+//                         bit positions of each table (:150-169)
+//   K3 bucket_*           per table: histogram of codes, exclusive scan, scatter of
+//                         the train indices -> CSR buckets            (:187-196)
+//   K4 probe_rerank_kernel per query: the 2^g probe codes of every table (:170-179),
+//                         the union of their buckets (:208-227), exact L1 top-2 of
+//                         those candidates on the uint8 rows           (:229-245)
+//
+// Exactness.  Rows are integers in [-128, 127] (exact in bf16).  The dictionary the
+// drop-in entry point draws is quantised to multiples of 1/32 in [-127/32, 127/32]
+// (exact in bf16), so every product is an integer multiple of 1/32 below 2^14 and
+// every partial sum is exact in fp32 in ANY order: the tensor-core projection, a
+// CPU float loop and Eigen's GEMM give identical signs, and codes are bit-exact
+// against the oracle.  An arbitrary fp32 dictionary (device API, golden vectors
+// produced by the reference's own generator) is split into three bf16 terms whose
+// sum is the fp32 value exactly; the projection then differs from an fp32 CPU loop
+// only by fp32 summation rounding, i.e. possibly in the sign of |R| < ~1e-3.
+#include "spv_common.h"
+
+#include <cuda_bf16.h>
+#include <cstdint>
+
+namespace spv {
+namespace {
+
+// ------------------------------------------------------------------ PTX glue
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 24)) {   // a protocol bug must trap, never hang the device
+      printf("cascade: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+
+// UMMA shared-memory matrix descriptor, K-major, no swizzle (canonical layout in
+// 16-byte units ((8, n), 2) : ((1, SBO), LBO)): 8 rows x 16 B core matrices, SBO =
+// byte stride between 8-row groups, LBO = byte stride between the two 8-element K
+// halves of one K=16 step.  Bits: [0,14) addr>>4, [16,30) LBO>>4, [32,46) SBO>>4,
+// [46,48) version = 1 (Blackwell), [61,64) layout type = 0 (no swizzle).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+// instruction descriptor, kind::f16: D fp32 (bits[4,6) = 1), A, B bf16 (bits[7,10) =
+// bits[10,13) = 1), both K-major (bits 15, 16 = 0), N >> 3 at [17,23), M >> 4 at [24,29)
+__device__ __forceinline__ uint32_t umma_idesc_bf16(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ---------------------------------------------------------------- K0
+// CascadingHashNn.h:236-239: cast<uint8_t>() then += 128 in uint8 arithmetic, i.e.
+// (uint8)((int)v + 128) for the integer-valued rows the Python wrapper passes.
+__global__ void f32_to_u8_kernel(const float4* __restrict__ in, uint32_t* __restrict__ out, size_t n4) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const float4 v = in[i];
+  const uint32_t b0 = (uint32_t)((int)v.x + 128) & 0xFF, b1 = (uint32_t)((int)v.y + 128) & 0xFF;
+  const uint32_t b2 = (uint32_t)((int)v.z + 128) & 0xFF, b3 = (uint32_t)((int)v.w + 128) & 0xFF;
+  out[i] = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+}
+
+// ---------------------------------------------------------------- dictionary image
+// dict [n][dim][m] fp32 (hash_dict(i, j), CascadingHashNn.h:93-97) -> the B operand
+// as it sits in shared memory: for every group of tables, three bf16 terms
+// (hi, mid, lo; hi + mid + lo == the fp32 value), each [dim/8 k-chunks][N][8 elems]
+// with column N-index = table_in_group * MP + bit, zero for padding columns.
+__global__ void dict_image_kernel(const float* __restrict__ dict, int n, int dim, int m, int MP, int tables_per_group,
+                                  int N, __nv_bfloat16* __restrict__ img) {
+  const int groups = (n + tables_per_group - 1) / tables_per_group;
+  const size_t per_term = (size_t)(dim / 8) * N * 8;
+  const size_t total = (size_t)groups * 3 * per_term;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(e / (3 * per_term));
+    const int term = (int)((e / per_term) % 3);
+    const size_t r = e % per_term;
+    const int kc = (int)(r / ((size_t)N * 8)), col = (int)((r / 8) % N), ke = (int)(r % 8);
+    const int t = g * tables_per_group + col / MP, bit = col % MP, k = kc * 8 + ke;
+    float v = 0.f;
+    if (col / MP < tables_per_group && t < n && bit < m) v = dict[((size_t)t * dim + k) * m + bit];
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    const float r1 = v - __bfloat162float(hi);
+    const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
+    const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
+    img[e] = term == 0 ? hi : term == 1 ? mid : lo;
+  }
+}
+
+// ---------------------------------------------------------------- K2
+constexpr int HP_ROWS = 128;     // rows per tile = UMMA M
+constexpr int HP_KPANEL = 128;   // columns of A staged per pass (16 k-chunks of 8)
+constexpr int HP_THREADS = 128;  // 4 warps: warp w owns TMEM lanes 32 w .. 32 w + 31
+
+struct HpParams {
+  const uint8_t* rows_u8;        // [rows][dim], value + 128
+  const __nv_bfloat16* img;      // dictionary image (dict_image_kernel)
+  int rows, dim, n, m, MP, tpg, N, groups, terms;
+  int g;                         // > 0: query mode, also emit the g least-confident bits
+  int32_t* codes;                // [n][rows]
+  unsigned long long* flips;     // [n][rows], 5 bits per position (query mode)
+  int tmem_cols;
+};
+
+template <int MP>
+__device__ __forceinline__ void hp_epilogue_table(uint32_t taddr, int m, int g, int32_t* code_out,
+                                                  unsigned long long* flip_out) {
+  float v[MP];
+#pragma unroll
+  for (int c = 0; c < MP; c += 8) {
+    float t8[8];
+    tmem_ld8(taddr + c, t8);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[c + i] = t8[i];
+  }
+  // convert_to_hashcode (CascadingHashNn.h:102-111): bit i set iff R(i) >= 0
+  uint32_t code = 0;
+#pragma unroll
+  for (int b = 0; b < MP; ++b)
+    if (b < m && v[b] >= 0.f) code |= 1u << b;
+  *code_out = (int32_t)code;
+  if (g > 0) {
+    // generate_y_candidate_hashcodes (:153-159): the g smallest (|R|, bit) pairs
+    uint32_t taken = 0;
+    unsigned long long flips = 0;
+    const int nb = g < m ? g : m;
+    for (int q = 0; q < nb; ++q) {
+      float best = __int_as_float(0x7f800000);
+      int bi = 0;
+      bool found = false;
+#pragma unroll
+      for (int b = 0; b < MP; ++b) {
+        const float a = fabsf(v[b]);
+        if (b < m && !((taken >> b) & 1u) && (!found || a < best)) { best = a; bi = b; found = true; }
+      }
+      taken |= 1u << bi;
+      flips |= (unsigned long long)bi << (5 * q);
+    }
+    *flip_out = flips;
+  }
+}
+
+__global__ void __launch_bounds__(HP_THREADS) hash_project_kernel(const HpParams P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int dim = P.dim, nkc = dim / 8, N = P.N;
+  const int bterm_bytes = nkc * N * 16;                      // one bf16 term of one group
+  unsigned char* sB = smem;                                  // [terms][nkc][N][16 B]
+  unsigned char* sA = sB + (size_t)P.terms * bterm_bytes;    // [16 k-chunks][128 rows][16 B]
+  unsigned long long* bar = reinterpret_cast<unsigned long long*>(sA + (HP_KPANEL / 8) * HP_ROWS * 16);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  if (tid == 0) {
+    mbar_init(smem_u32(bar), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(P.tmem_cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t idesc = umma_idesc_bf16(HP_ROWS, N);
+  const int ntiles = (P.rows + HP_ROWS - 1) / HP_ROWS;
+  const int npanels = (dim + HP_KPANEL - 1) / HP_KPANEL;
+  uint32_t parity = 0;
+
+  for (int grp = 0; grp < P.groups; ++grp) {
+    // B operand of this group of tables: a straight copy of the prepared image
+    {
+      const uint4* src = reinterpret_cast<const uint4*>(P.img) + (size_t)grp * 3 * (bterm_bytes / 16);
+      uint4* dst = reinterpret_cast<uint4*>(sB);
+      for (int term = 0; term < P.terms; ++term)
+        for (int e = tid; e < bterm_bytes / 16; e += HP_THREADS)
+          dst[(size_t)term * (bterm_bytes / 16) + e] = src[(size_t)term * (bterm_bytes / 16) + e];
+    }
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int row0 = tile * HP_ROWS;
+      for (int pn = 0; pn < npanels; ++pn) {
+        const int c0 = pn * HP_KPANEL;                        // first column of the panel
+        const int pcols = min(HP_KPANEL, dim - c0);           // multiple of 16
+        const int p16 = pcols / 16;                           // 16-byte input chunks per row
+        // stage A: uint8 (value + 128) -> bf16 value, k-chunk-major
+        for (int e = tid; e < HP_ROWS * p16; e += HP_THREADS) {
+          const int r = e / p16, j = e % p16;
+          uint4 raw = make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);   // zero rows
+          if (row0 + r < P.rows) raw = *reinterpret_cast<const uint4*>(P.rows_u8 + (size_t)(row0 + r) * dim + c0 + j * 16);
+          const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+          uint32_t o[8];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float f0 = (float)((int)(w[q] & 0xFF) - 128), f1 = (float)((int)((w[q] >> 8) & 0xFF) - 128);
+            const float f2 = (float)((int)((w[q] >> 16) & 0xFF) - 128), f3 = (float)((int)(w[q] >> 24) - 128);
+            __nv_bfloat162 lo2 = __floats2bfloat162_rn(f0, f1), hi2 = __floats2bfloat162_rn(f2, f3);
+            o[2 * q] = *reinterpret_cast<uint32_t*>(&lo2);
+            o[2 * q + 1] = *reinterpret_cast<uint32_t*>(&hi2);
+          }
+          *reinterpret_cast<uint4*>(sA + ((size_t)(2 * j) * HP_ROWS + r) * 16) = make_uint4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<uint4*>(sA + ((size_t)(2 * j + 1) * HP_ROWS + r) * 16) = make_uint4(o[4], o[5], o[6], o[7]);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+          for (int term = 0; term < P.terms; ++term)
+            for (int s = 0; s < pcols / 16; ++s) {              // one UMMA per K = 16
+              const uint64_t ad = umma_desc(a0 + (2 * s) * (HP_ROWS * 16), HP_ROWS * 16, 128);
+              const uint64_t bd = umma_desc(b0 + term * bterm_bytes + (c0 / 8 + 2 * s) * (N * 16), N * 16, 128);
+              umma_bf16(tmem, ad, bd, idesc, (pn | term | s) != 0);
+            }
+          umma_commit(smem_u32(bar));   // implies tcgen05.fence::before_thread_sync
+        }
+        mbar_wait(smem_u32(bar), parity);   // MMAs done: A may be overwritten, D may be read
+        parity ^= 1;
+      }
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      // epilogue: thread = row (TMEM lane), columns [t_in_group * MP, + MP)
+      const int row = row0 + tid;
+      for (int tg = 0; tg < P.tpg; ++tg) {
+        const int t = grp * P.tpg + tg;
+        if (t >= P.n) break;
+        const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + tg * P.MP;
+        int32_t code;
+        unsigned long long fl = 0;
+        if (P.MP == 8) hp_epilogue_table<8>(taddr, P.m, P.g, &code, &fl);
+        else if (P.MP == 16) hp_epilogue_table<16>(taddr, P.m, P.g, &code, &fl);
+        else if (P.MP == 24) hp_epilogue_table<24>(taddr, P.m, P.g, &code, &fl);
+        else hp_epilogue_table<32>(taddr, P.m, P.g, &code, &fl);
+        if (row < P.rows) {
+          P.codes[(size_t)t * P.rows + row] = code;
+          if (P.g > 0) P.flips[(size_t)t * P.rows + row] = fl;
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();   // everyone is done with sB before the next group's image lands
+  }
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(P.tmem_cols) : "memory");
+}
+
+// ---------------------------------------------------------------- K3: CSR buckets
+// Bucket key = code & (2^mb - 1), mb = min(m, 24) (full codes are re-checked in K4
+// when m > 24).  All tables share one count/offset array of n * 2^mb entries and
+// one id array of n * xrows entries, so a single scan serves every table.
+__global__ void bucket_count_kernel(const int32_t* __restrict__ codes, size_t total, int xrows, uint32_t mask, int mb,
+                                    uint32_t* __restrict__ cnt) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= total) return;
+  const size_t t = e / xrows;
+  atomicAdd(&cnt[(t << mb) + ((uint32_t)codes[e] & mask)], 1u);
+}
+
+constexpr int SCAN_BLOCK = 256, SCAN_ITEMS = 8, SCAN_TILE = SCAN_BLOCK * SCAN_ITEMS;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total, uint32_t* ws) {
+  // ws: SCAN_BLOCK / 32 + 1 words of shared memory
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) ws[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < SCAN_BLOCK / 32 ? ws[lane] : 0, winc = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, winc, d);
+      if (lane >= d) winc += o;
+    }
+    if (lane < SCAN_BLOCK / 32) ws[lane] = winc - w;
+    if (lane == 31) ws[SCAN_BLOCK / 32] = winc;
+  }
+  __syncthreads();
+  *total = ws[SCAN_BLOCK / 32];
+  const uint32_t r = ws[warp] + inc - v;
+  __syncthreads();
+  return r;
+}
+
+// phase 1: per-tile sums; phase 3 (apply = true): in-place exclusive scan + tile offset
+__global__ void __launch_bounds__(SCAN_BLOCK) scan_tiles_kernel(uint32_t* __restrict__ data, size_t n,
+                                                                uint32_t* __restrict__ tile_sums, bool apply) {
+  __shared__ uint32_t ws[SCAN_BLOCK / 32 + 1];
+  const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+  uint32_t v[SCAN_ITEMS], s = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) { v[i] = base + i < n ? data[base + i] : 0; s += v[i]; }
+  uint32_t total;
+  uint32_t ex = block_exclusive_scan(s, &total, ws);
+  if (!apply) {
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+    return;
+  }
+  ex += tile_sums[blockIdx.x];
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) {
+    if (base + i < n) data[base + i] = ex;
+    ex += v[i];
+  }
+}
+
+// phase 2: exclusive scan of the tile sums by one block
+__global__ void __launch_bounds__(SCAN_BLOCK) scan_sums_kernel(uint32_t* __restrict__ sums, int n) {
+  __shared__ uint32_t ws[SCAN_BLOCK / 32 + 1];
+  uint32_t carry = 0;
+  for (int b0 = 0; b0 < n; b0 += SCAN_BLOCK) {
+    const int i = b0 + threadIdx.x;
+    const uint32_t v = i < n ? sums[i] : 0;
+    uint32_t total;
+    const uint32_t ex = block_exclusive_scan(v, &total, ws);
+    if (i < n) sums[i] = carry + ex;
+    carry += total;
+  }
+}
+
+// scatter: cursor starts as the bucket's begin offset and ends as its end offset,
+// so afterwards  begin(b) = b ? cursor[b - 1] : 0,  end(b) = cursor[b]  over the
+// concatenated (table, bucket) axis.  Order inside a bucket is arbitrary; K4's
+// result does not depend on it (lexicographic (dist, idx) top-2).
+__global__ void bucket_scatter_kernel(const int32_t* __restrict__ codes, size_t total, int xrows, uint32_t mask, int mb,
+                                      uint32_t* __restrict__ cursor, int32_t* __restrict__ ids) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= total) return;
+  const size_t t = e / xrows;
+  const uint32_t pos = atomicAdd(&cursor[(t << mb) + ((uint32_t)codes[e] & mask)], 1u);
+  ids[pos] = (int32_t)(e - t * xrows);
+}
+
+// ---------------------------------------------------------------- K4
+constexpr int PR_WARPS = 8;      // query rows per CTA (one warp each)
+constexpr int PR_LCAP = 256;     // candidate ids staged per warp before a distance pass
+
+struct PrParams {
+  const uint8_t* xu8;            // [xrows][dim]
+  const uint8_t* yu8;            // [yrows][dim]
+  const int32_t* xcodes;         // [n][xrows]   (full codes, consulted only when m > mb)
+  const int32_t* ycodes;         // [n][yrows]
+  const unsigned long long* yflips;   // [n][yrows]
+  const uint32_t* cursor;        // [n << mb] bucket END offsets over the concatenated axis
+  const int32_t* ids;            // [n * xrows]
+  int xrows, yrows, dim, n, m, mb, nb;
+  uint32_t xoffset;
+  unsigned long long* keys;      // [2][yrows]
+};
+
+// the two smallest DISTINCT keys of {a1 < a2} U {b1 < b2}; equal keys are the same
+// (dist, idx) reached through two tables / probes -- the reference's unordered_set
+// (CascadingHashNn.h:223) removes exactly those
+__device__ __forceinline__ void top2_merge(unsigned long long& a1, unsigned long long& a2, unsigned long long b1,
+                                           unsigned long long b2) {
+  const unsigned long long lo = a1 < b1 ? a1 : b1;
+  unsigned long long hi = a1 < b1 ? b1 : a1;
+  if (hi == lo) hi = KEY_NONE;
+  unsigned long long s = a2 < b2 ? a2 : b2;
+  s = hi < s ? hi : s;
+  a1 = lo;
+  a2 = s;
+}
+
+__global__ void __launch_bounds__(PR_WARPS * 32) probe_rerank_kernel(const PrParams P) {
+  __shared__ int32_t lists[PR_WARPS][PR_LCAP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 3, l8 = lane & 7;
+  const int r = blockIdx.x * PR_WARPS + warp;
+  if (r >= P.yrows) return;   // whole warp
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int nk16 = P.dim / 16;
+  const uint32_t mask = (P.mb >= 32) ? 0xFFFFFFFFu : ((1u << P.mb) - 1u);
+  const bool verify = P.m > P.mb;
+  int32_t* list = lists[warp];
+
+  // this lane's 16-byte slices of the query row: chunks l8, l8 + 8, ...
+  uint4 yv[4];
+  const uint4* yrow = reinterpret_cast<const uint4*>(P.yu8 + (size_t)r * P.dim);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
+
+  unsigned long long k1 = KEY_NONE, k2 = KEY_NONE;
+
+  // L1 distance of train row `id` to the query row by the 8 lanes of a group; id < 0: skip
+  auto offer = [&](int id) {
+    uint32_t d = 0;
+    if (id >= 0) {
+      const uint4* xr = reinterpret_cast<const uint4*>(P.xu8 + (size_t)id * P.dim);
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (l8 + 8 * c < nk16) {
+          const uint4 v = __ldg(xr + l8 + 8 * c);
+          d = sad4(v.x, yv[c].x, d); d = sad4(v.y, yv[c].y, d);
+          d = sad4(v.z, yv[c].z, d); d = sad4(v.w, yv[c].w, d);
+        }
+    }
+    d += __shfl_xor_sync(FULL, d, 1);
+    d += __shfl_xor_sync(FULL, d, 2);
+    d += __shfl_xor_sync(FULL, d, 4);
+    if (id >= 0) {
+      const unsigned long long key = ((unsigned long long)d << 32) | (uint32_t)(P.xoffset + (uint32_t)id);
+      if (key < k1) { k2 = k1; k1 = key; }
+      else if (key != k1 && key < k2) k2 = key;
+    }
+  };
+  auto drain = [&](int count) {
+    __syncwarp();
+    for (int c0 = 0; c0 < count; c0 += 4) offer(c0 + grp < count ? list[c0 + grp] : -1);
+    __syncwarp();
+  };
+
+  const int P_total = P.n << P.nb;   // probe codes of this query: n tables x 2^nb settings
+  int listn = 0;
+  for (int p0 = 0; p0 < P_total; p0 += 32) {
+    const int p = p0 + lane;
+    uint32_t start = 0, len = 0;
+    int t = 0;
+    uint32_t code = 0;
+    if (p < P_total) {
+      t = p >> P.nb;
+      const uint32_t combo = (uint32_t)p & ((1u << P.nb) - 1u);
+      code = (uint32_t)P.ycodes[(size_t)t * P.yrows + r];
+      const unsigned long long fl = P.yflips[(size_t)t * P.yrows + r];
+      for (int q = 0; q < P.nb; ++q) {   // generate_y_candidate_hashcodes :170-179
+        const uint32_t bit = (uint32_t)(fl >> (5 * q)) & 31u;
+        code = (code & ~(1u << bit)) | (((combo >> q) & 1u) << bit);
+      }
+      const size_t b = ((size_t)t << P.mb) + (code & mask);
+      const uint32_t end = P.cursor[b];
+      start = b ? P.cursor[b - 1] : 0u;
+      len = end - start;
+    }
+    // exclusive prefix of len over the warp
+    uint32_t inc = len;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(FULL, inc, d);
+      if (lane >= d) inc += o;
+    }
+    const uint32_t T = __shfl_sync(FULL, inc, 31), off = inc - len;
+    if (T == 0) continue;
+    if (listn + (int)T > PR_LCAP) { drain(listn); listn = 0; }
+    if ((int)T <= PR_LCAP) {
+      for (uint32_t i = 0; i < len; ++i) {
+        int id = P.ids[start + i];
+        if (verify && (uint32_t)P.xcodes[(size_t)t * P.xrows + id] != code) id = -1;
+        list[listn + off + i] = id;
+      }
+      listn += (int)T;
+    } else {
+      // very full buckets: take the lanes' ranges one after the other, straight from global memory
+      for (int src = 0; src < 32; ++src) {
+        const uint32_t s_start = __shfl_sync(FULL, start, src), s_len = __shfl_sync(FULL, len, src);
+        const uint32_t s_code = __shfl_sync(FULL, code, src);
+        const int s_t = __shfl_sync(FULL, t, src);
+        for (uint32_t c0 = 0; c0 < s_len; c0 += 4) {
+          int id = -1;
+          if (c0 + grp < s_len) {
+            id = P.ids[s_start + c0 + grp];
+            if (verify && (uint32_t)P.xcodes[(size_t)s_t * P.xrows + id] != s_code) id = -1;
+          }
+          offer(id);
+        }
+      }
+    }
+  }
+  drain(listn);
+
+  // the four lane groups hold disjoint-or-duplicate candidate subsets
+#pragma unroll
+  for (int d = 8; d <= 16; d <<= 1) {
+    const unsigned long long o1 = __shfl_xor_sync(FULL, k1, d), o2 = __shfl_xor_sync(FULL, k2, d);
+    top2_merge(k1, k2, o1, o2);
+  }
+  if (lane == 0) {   // fold into what other train shards / launches left there
+    unsigned long long e1 = P.keys[r], e2 = P.keys[(size_t)P.yrows + r];
+    top2_merge(e1, e2, k1, k2);
+    P.keys[r] = e1;
+    P.keys[(size_t)P.yrows + r] = e2;
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+namespace {
+
+struct Plan {
+  int MP, tpg, N, groups, tmem_cols, mb, nb, terms;
+  size_t smem_hp;
+  // workspace offsets (bytes)
+  size_t o_img, o_xcodes, o_ycodes, o_yflips, o_cursor, o_ids, o_sums, total;
+  size_t ncursor;
+  int nsum_tiles;
+};
+
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+bool make_plan(int xrows, int yrows, int dim, int m, int n, int g, int terms, Plan* pl) {
+  if (dim < 16 || dim % 16 != 0 || dim > 512 || m < 1 || m > 31 || n < 1 || g < 0) return false;
+  pl->terms = terms;
+  pl->nb = g < m ? g : m;                       // :153-159 keeps at most m pairs
+  if (pl->nb > 12 || ((long long)n << pl->nb) > (1ll << 24)) return false;
+  pl->mb = m < 24 ? m : 24;
+  pl->MP = (m + 7) / 8 * 8;
+  const int nkc = dim / 8;
+  const size_t a_bytes = (size_t)(HP_KPANEL / 8) * HP_ROWS * 16, budget = 190 * 1024;
+  int nmax = (int)((budget - a_bytes - 64) / ((size_t)terms * nkc * 16)) / 16 * 16;
+  if (nmax > 256) nmax = 256;
+  int tpg = nmax / pl->MP;
+  if (tpg > n) tpg = n;
+  if (tpg > 4 && n > 4) tpg = 4;                // keep the B image small enough for several CTAs per SM
+  if (tpg < 1) return false;
+  pl->tpg = tpg;
+  pl->N = (tpg * pl->MP + 15) / 16 * 16;
+  pl->groups = (n + tpg - 1) / tpg;
+  int cols = 32;
+  while (cols < pl->N) cols <<= 1;
+  pl->tmem_cols = cols;
+  pl->smem_hp = (size_t)terms * nkc * pl->N * 16 + a_bytes + 64;
+  pl->ncursor = (size_t)n << pl->mb;
+  pl->nsum_tiles = (int)((pl->ncursor + SCAN_TILE - 1) / SCAN_TILE);
+  size_t o = 0;
+  pl->o_img = o;     o = align256(o + (size_t)pl->groups * 3 * nkc * pl->N * 8 * sizeof(__nv_bfloat16));
+  pl->o_xcodes = o;  o = align256(o + (size_t)n * (xrows > 0 ? xrows : 1) * 4);
+  pl->o_ycodes = o;  o = align256(o + (size_t)n * (yrows > 0 ? yrows : 1) * 4);
+  pl->o_yflips = o;  o = align256(o + (size_t)n * (yrows > 0 ? yrows : 1) * 8);
+  pl->o_cursor = o;  o = align256(o + pl->ncursor * 4);
+  pl->o_ids = o;     o = align256(o + (size_t)n * (xrows > 0 ? xrows : 1) * 4);
+  pl->o_sums = o;    o = align256(o + (size_t)pl->nsum_tiles * 4 + 4);
+  pl->total = o;
+  return true;
+}
+
+cudaError_t run_project(const Plan& pl, const uint8_t* rows_u8, int rows, int dim, int n, int m, int g,
+                        const __nv_bfloat16* img, int32_t* codes, unsigned long long* flips, int sms, cudaStream_t stream) {
+  if (rows <= 0) return cudaSuccess;
+  HpParams hp;
+  hp.rows_u8 = rows_u8; hp.img = img; hp.rows = rows; hp.dim = dim; hp.n = n; hp.m = m; hp.MP = pl.MP; hp.tpg = pl.tpg;
+  hp.N = pl.N; hp.groups = pl.groups; hp.terms = pl.terms; hp.g = g; hp.codes = codes; hp.flips = flips;
+  hp.tmem_cols = pl.tmem_cols;
+  cudaError_t e = cudaFuncSetAttribute(hash_project_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_hp);
+  if (e != cudaSuccess) return e;
+  int per_sm = (int)((200 * 1024) / (pl.smem_hp + 1024));
+  if (per_sm > 512 / pl.tmem_cols) per_sm = 512 / pl.tmem_cols;   // TMEM columns are a per-SM resource
+  if (per_sm > 4) per_sm = 4;
+  if (per_sm < 1) per_sm = 1;
+  const int ntiles = (rows + HP_ROWS - 1) / HP_ROWS;
+  const int grid = ntiles < sms * per_sm ? ntiles : sms * per_sm;
+  hash_project_kernel<<<grid, HP_THREADS, pl.smem_hp, stream>>>(hp);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+size_t cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g) {
+  Plan pl;
+  if (!make_plan(xrows, yrows, dim, m, n, g, 3, &pl)) return 0;
+  return pl.total;
+}
+
+cudaError_t f32_to_u8(const float* din, uint8_t* dout, size_t count, cudaStream_t stream) {
+  if (count == 0) return cudaSuccess;
+  if (count % 4) return cudaErrorInvalidValue;   // rows are multiples of 16 columns
+  const size_t n4 = count / 4;
+  f32_to_u8_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, stream>>>(reinterpret_cast<const float4*>(din),
+                                                                      reinterpret_cast<uint32_t*>(dout), n4);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, int yrows, int dim, int m, int n, int g,
+                          const float* ddict, int dict_terms, uint32_t xoffset, unsigned long long* keys, void* ws,
+                          size_t ws_bytes, cudaStream_t stream) {
+  if (yrows <= 0 || xrows <= 0) return cudaSuccess;   // nothing to fold in
+  Plan pl;
+  if (dict_terms != 1 && dict_terms != 3) return cudaErrorInvalidValue;
+  if (!make_plan(xrows, yrows, dim, m, n, g, dict_terms, &pl) || ws_bytes < pl.total) return cudaErrorInvalidValue;
+  int dev = 0, sms = 0;
+  cudaError_t e;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  unsigned char* w = static_cast<unsigned char*>(ws);
+  __nv_bfloat16* img = reinterpret_cast<__nv_bfloat16*>(w + pl.o_img);
+  int32_t* xcodes = reinterpret_cast<int32_t*>(w + pl.o_xcodes);
+  int32_t* ycodes = reinterpret_cast<int32_t*>(w + pl.o_ycodes);
+  unsigned long long* yflips = reinterpret_cast<unsigned long long*>(w + pl.o_yflips);
+  uint32_t* cursor = reinterpret_cast<uint32_t*>(w + pl.o_cursor);
+  int32_t* ids = reinterpret_cast<int32_t*>(w + pl.o_ids);
+  uint32_t* sums = reinterpret_cast<uint32_t*>(w + pl.o_sums);
+
+  dict_image_kernel<<<64, 256, 0, stream>>>(ddict, n, dim, m, pl.MP, pl.tpg, pl.N, img);
+  count_launch();
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  // train side: codes, then CSR buckets (initialize_hash_tables, :187-196)
+  if ((e = run_project(pl, dxu8, xrows, dim, n, m, 0, img, xcodes, nullptr, sms, stream)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(cursor, 0, pl.ncursor * 4, stream)) != cudaSuccess) return e;
+  const size_t total = (size_t)n * xrows;
+  const uint32_t mask = (1u << pl.mb) - 1u;
+  bucket_count_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(xcodes, total, xrows, mask, pl.mb, cursor);
+  scan_tiles_kernel<<<pl.nsum_tiles, SCAN_BLOCK, 0, stream>>>(cursor, pl.ncursor, sums, false);
+  scan_sums_kernel<<<1, SCAN_BLOCK, 0, stream>>>(sums, pl.nsum_tiles);
+  scan_tiles_kernel<<<pl.nsum_tiles, SCAN_BLOCK, 0, stream>>>(cursor, pl.ncursor, sums, true);
+  bucket_scatter_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(xcodes, total, xrows, mask, pl.mb, cursor, ids);
+  count_launch(5);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  // query side: codes + least-confident bits, then probe / gather / re-rank
+  if ((e = run_project(pl, dyu8, yrows, dim, n, m, pl.nb > 0 ? pl.nb : 0, img, ycodes, yflips, sms, stream)) != cudaSuccess) return e;
+  if (pl.nb == 0 && (e = cudaMemsetAsync(yflips, 0, (size_t)n * yrows * 8, stream)) != cudaSuccess) return e;
+  PrParams pr;
+  pr.xu8 = dxu8; pr.yu8 = dyu8; pr.xcodes = xcodes; pr.ycodes = ycodes; pr.yflips = yflips; pr.cursor = cursor; pr.ids = ids;
+  pr.xrows = xrows; pr.yrows = yrows; pr.dim = dim; pr.n = n; pr.m = m; pr.mb = pl.mb; pr.nb = pl.nb; pr.xoffset = xoffset;
+  pr.keys = keys;
+  probe_rerank_kernel<<<(yrows + PR_WARPS - 1) / PR_WARPS, PR_WARPS * 32, 0, stream>>>(pr);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace spv

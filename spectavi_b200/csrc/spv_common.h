@@ -45,6 +45,15 @@ constexpr int LP_MAX_K = 128;
 size_t lp_partial_bytes(int xrows, int yrows, int k, int sms);
 cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
                     unsigned long long* partial, uint64_t* didx, void* ddist, cudaStream_t stream);
+// ---- cascade.cu : the cascade-of-hashes matcher (CascadingHashNn.h)
+// rows are uint8 (value + 128); ddict: [n][dim][m] fp32 on the device; dict_terms 1
+// when every entry is exact in bf16 (the library's own quantised dictionary), else 3.
+// Folds the top-2 of the candidates of dy among dx[0..xrows) into keys.
+size_t cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g);
+cudaError_t f32_to_u8(const float* din, uint8_t* dout, size_t count, cudaStream_t stream);
+cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, int yrows, int dim, int m, int n, int g,
+                          const float* ddict, int dict_terms, uint32_t xoffset, unsigned long long* keys, void* ws,
+                          size_t ws_bytes, cudaStream_t stream);
 // launch count bookkeeping (bench.py's gpu_launches)
 unsigned long long launches();
 void count_launch(int n = 1);
