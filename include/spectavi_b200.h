@@ -94,6 +94,28 @@ int spv_keys_merge(uint64_t *dkeys, const uint64_t *dsrc, int nsrc, int yrows, v
 int spv_keys_finalize_i32(const uint64_t *dkeys, int yrows, int kcols, uint64_t *didx, int32_t *ddist, void *stream);
 int spv_keys_finalize_f32(const uint64_t *dkeys, int yrows, int kcols, uint64_t *didx, float *ddist, void *stream);
 
+/* K0: (uint8)((int)v + 128), the cast of CascadingHashNn.h:236-239 (count % 4 == 0) */
+int spv_f32_to_u8_device(const float *din, uint8_t *dout, size_t count, void *stream);
+/* scratch bytes spv_cascade_device needs (0 = unsupported parameters) */
+size_t spv_cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g);
+/* K2-K4: cascade-of-hashes match of uint8 (value + 128) query rows dyu8 against
+ * train rows dxu8 (replaces CascadingHashNn, src/CascadingHashNn.h:187-245), folded
+ * into dkeys like spv_l1k2_device.  ddict: device float32 [n][dim][m] hyperplanes;
+ * dict_terms: 1 if every entry is exact in bf16, else 3 (exact 3-term bf16 split). */
+int spv_cascade_device(const uint8_t *dxu8, const uint8_t *dyu8, int xrows, int yrows, int dim, int m, int n, int g,
+                       const float *ddict, int dict_terms, uint32_t xoffset, uint64_t *dkeys, void *dws,
+                       size_t ws_bytes, void *stream);
+/* K2 alone: hash codes [n][rows] int32 of uint8 (value + 128) rows (replaces
+ * generate_hashcodes_for_data, CascadingHashNn.h:125-135) and, when g > 0, the
+ * min(g, m) least-confident bit positions of every (table, row), 5 bits each
+ * (generate_y_candidate_hashcodes, :153-169); scratch as spv_cascade_ws_bytes(rows, rows, ...) */
+int spv_hash_codes_device(const uint8_t *drows, int rows, int dim, int m, int n, int g, const float *ddict,
+                          int dict_terms, int32_t *dcodes, uint64_t *dflips, void *dws, size_t ws_bytes, void *stream);
+/* the dictionary nn_cascading_hash draws (host): generate_hash_dict's loop order
+ * (CascadingHashNn.h:86-100) over std::mt19937(seed); quantize: multiples of 1/32 */
+void spv_cascade_dictionary(unsigned seed, int dim, int m, int n, int quantize, float *out);
+unsigned spv_cascade_seed(void);
+
 /* number of kernels this library has launched since it was loaded */
 uint64_t spv_launch_count(void);
 /* last error text of the calling thread's most recent failed spv_* call */

@@ -95,6 +95,37 @@ int spv_keys_finalize_f32(const uint64_t* dkeys, int yrows, int kcols, uint64_t*
   return 0;
 }
 
+int spv_f32_to_u8_device(const float* din, uint8_t* dout, size_t count, void* stream) {
+  CU_OR_FAIL(f32_to_u8(din, dout, count, (cudaStream_t)stream));
+  return 0;
+}
+
+size_t spv_cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g) {
+  return cascade_ws_bytes(xrows, yrows, dim, m, n, g);
+}
+
+int spv_cascade_device(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, int yrows, int dim, int m, int n, int g,
+                       const float* ddict, int dict_terms, uint32_t xoffset, uint64_t* dkeys, void* dws, size_t ws_bytes,
+                       void* stream) {
+  if (xrows < 0 || yrows < 0) return fail("negative row count");
+  CU_OR_FAIL(cascade_match(dxu8, dyu8, xrows, yrows, dim, m, n, g, ddict, dict_terms, xoffset,
+                           reinterpret_cast<unsigned long long*>(dkeys), dws, ws_bytes, (cudaStream_t)stream));
+  return 0;
+}
+
+int spv_hash_codes_device(const uint8_t* drows, int rows, int dim, int m, int n, int g, const float* ddict, int dict_terms,
+                          int32_t* dcodes, uint64_t* dflips, void* dws, size_t ws_bytes, void* stream) {
+  CU_OR_FAIL(hash_codes(drows, rows, dim, m, n, g, ddict, dict_terms, dcodes,
+                        reinterpret_cast<unsigned long long*>(dflips), dws, ws_bytes, (cudaStream_t)stream));
+  return 0;
+}
+
+void spv_cascade_dictionary(unsigned seed, int dim, int m, int n, int quantize, float* out) {
+  cascade_dictionary(seed, dim, m, n, quantize != 0, out);
+}
+
+unsigned spv_cascade_seed(void) { return cascade_seed(); }
+
 uint64_t spv_launch_count(void) { return launches(); }
 const char* spv_last_error(void) { return g_err; }
 
@@ -136,8 +167,20 @@ void nn_bruteforcei(const int* x, const int* y, int xrows, int yrows, int dim, i
   (void)mu;
   lp_entry("nn_bruteforcei", x, y, true, xrows, yrows, dim, k, p, outidx, outdist);
 }
-void nn_cascading_hash(const float*, const float*, int, int, int, int, int, int, int, NdArray*, NdArray*) {
-  die("nn_cascading_hash", "not built yet");
+void nn_cascading_hash(const float* x, const float* y, int xrows, int yrows, int dim, int k, int hash_bit_rate,
+                       int num_hash_tables, int num_candidate_neighbours, NdArray* outidx, NdArray* outdist) {
+  const char* fn = "nn_cascading_hash";
+  if (xrows < 0 || yrows < 0 || dim <= 0) die(fn, "bad shape %d x %d x %d", xrows, yrows, dim);
+  // the reference sizes its outputs yrows x k but assigns a yrows x 2 matrix to them
+  // (CascadingHashNn.h:244): only k == 2 is well defined there; k > 2 leaves columns >= 2 zero here
+  if (k < 2) die(fn, "k = %d: the matcher always produces 2 neighbours (CascadingHashNn.h:229-245)", k);
+  out_alloc(outidx, (uint64_t)yrows, (uint64_t)k);     // Spectavi.cpp:329-332
+  out_alloc(outdist, (uint64_t)yrows, (uint64_t)k);
+  if (dim % 16 != 0) die(fn, "data dimension (%d) must be a multiple of 16", dim);   // BruteForceNnL1K2.h:78-81
+  if (yrows == 0) return;
+  HostCall hc(fn);
+  hc.cascade(x, y, xrows, yrows, dim, k, hash_bit_rate, num_hash_tables, num_candidate_neighbours,
+             reinterpret_cast<uint64_t*>(outidx->m_data), reinterpret_cast<float*>(outdist->m_data));
 }
 
 }  // extern "C"

@@ -621,6 +621,24 @@ cudaError_t f32_to_u8(const float* din, uint8_t* dout, size_t count, cudaStream_
   return cudaGetLastError();
 }
 
+// K2 alone (tests, profiling): codes [n][rows] and, when g > 0, flips [n][rows]
+cudaError_t hash_codes(const uint8_t* drows, int rows, int dim, int m, int n, int g, const float* ddict, int dict_terms,
+                       int32_t* codes, unsigned long long* flips, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  if (rows <= 0) return cudaSuccess;
+  Plan pl;
+  if (dict_terms != 1 && dict_terms != 3) return cudaErrorInvalidValue;
+  if (!make_plan(rows, rows, dim, m, n, g, dict_terms, &pl) || ws_bytes < pl.total) return cudaErrorInvalidValue;
+  int dev = 0, sms = 0;
+  cudaError_t e;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  __nv_bfloat16* img = reinterpret_cast<__nv_bfloat16*>(static_cast<unsigned char*>(ws) + pl.o_img);
+  dict_image_kernel<<<64, 256, 0, stream>>>(ddict, n, dim, m, pl.MP, pl.tpg, pl.N, img);
+  count_launch();
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  return run_project(pl, drows, rows, dim, n, m, g > 0 ? pl.nb : 0, img, codes, flips, sms, stream);
+}
+
 cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, int yrows, int dim, int m, int n, int g,
                           const float* ddict, int dict_terms, uint32_t xoffset, unsigned long long* keys, void* ws,
                           size_t ws_bytes, cudaStream_t stream) {

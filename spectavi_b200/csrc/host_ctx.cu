@@ -5,7 +5,9 @@
 #include <dlfcn.h>
 #include <nccl.h>   // types only; the library is dlopen()ed when SPECTAVI_GPUS > 1
 
+#include <cmath>
 #include <cstdlib>
+#include <random>
 #include <cstring>
 #include <vector>
 
@@ -31,7 +33,7 @@ struct Buf {
 struct Gpu {
   int dev = -1;
   cudaStream_t stream = nullptr;
-  Buf x, y, keys, gather, oidx, odist;
+  Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws;
 };
 
 struct Nccl {
@@ -175,6 +177,106 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
   for (int g = 0; g < G; ++g) {
     CU(fn_, cudaSetDevice(g_rt.gpus[g].dev));
     CU(fn_, cudaStreamSynchronize(g_rt.gpus[g].stream));
+  }
+  cudaSetDevice(prev);
+}
+
+void cascade_dictionary(unsigned seed, int dim, int m, int n, bool quantize, float* out) {
+  std::mt19937 gen(seed);
+  std::normal_distribution<float> normal(0.f, 1.f);
+  for (int t = 0; t < n; ++t)
+    for (int i = 0; i < dim; ++i)
+      for (int j = 0; j < m; ++j) {
+        float v = normal(gen);
+        if (quantize) {
+          float q = nearbyintf(v * 32.f);
+          q = q > 127.f ? 127.f : (q < -127.f ? -127.f : q);
+          v = q / 32.f;
+        }
+        out[((size_t)t * dim + i) * m + j] = v;
+      }
+}
+
+unsigned cascade_seed() {
+  if (const char* s = getenv("SPECTAVI_SEED")) return (unsigned)strtoul(s, nullptr, 0);
+  return 0x5EED5EEDu;
+}
+
+void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
+                       uint64_t* idx, float* dist) {
+  const int G = (int)g_rt.gpus.size();
+  const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
+  const int per = (xrows + G - 1) / G;   // train rows per GPU, as for brute force
+  std::vector<float> hdict((size_t)n * dim * m);
+  cascade_dictionary(cascade_seed(), dim, m, n, true, hdict.data());
+  int prev = 0;
+  cudaGetDevice(&prev);
+  for (int gi = 0; gi < G; ++gi) {
+    Gpu& D = g_rt.gpus[gi];
+    CU(fn_, cudaSetDevice(D.dev));
+    const int x0 = gi * per < xrows ? gi * per : xrows;
+    const int xn = (x0 + per <= xrows) ? per : xrows - x0;
+    const size_t wsb = cascade_ws_bytes(xn, yrows, dim, m, n, g);
+    if (wsb == 0) die(fn_, "unsupported parameters dim=%d m=%d n=%d g=%d (need dim %% 16 == 0, dim <= 512, 1 <= m <= 31, g <= 12)", dim, m, n, g);
+    CU(fn_, D.y.ensure(ybytes));
+    CU(fn_, D.keys.ensure(kbytes));
+    CU(fn_, D.dict.ensure(hdict.size() * 4));
+    CU(fn_, D.ws.ensure(wsb));
+    CU(fn_, cudaMemcpyAsync(D.dict.p, hdict.data(), hdict.size() * 4, cudaMemcpyHostToDevice, D.stream));
+    if (xn > 0) {
+      CU(fn_, D.xf.ensure((size_t)xn * dim * 4));
+      CU(fn_, D.x.ensure((size_t)xn * dim));
+      CU(fn_, cudaMemcpyAsync(D.xf.p, x + (size_t)x0 * dim, (size_t)xn * dim * 4, cudaMemcpyHostToDevice, D.stream));
+      CU(fn_, f32_to_u8((const float*)D.xf.p, (uint8_t*)D.x.p, (size_t)xn * dim, D.stream));   // CascadingHashNn.h:236-239
+    }
+    if (gi == 0) {
+      CU(fn_, D.yf.ensure(ybytes * 4));
+      CU(fn_, cudaMemcpyAsync(D.yf.p, y, ybytes * 4, cudaMemcpyHostToDevice, D.stream));
+      CU(fn_, f32_to_u8((const float*)D.yf.p, (uint8_t*)D.y.p, ybytes, D.stream));
+    }
+    CU(fn_, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
+  }
+  if (G > 1) {
+    NC(fn_, g_rt.nccl.GroupStart());
+    for (int gi = 0; gi < G; ++gi)
+      NC(fn_, g_rt.nccl.Broadcast(g_rt.gpus[0].y.p, g_rt.gpus[gi].y.p, ybytes, ncclUint8, 0, g_rt.nccl.comms[gi],
+                                  g_rt.gpus[gi].stream));
+    NC(fn_, g_rt.nccl.GroupEnd());
+  }
+  for (int gi = 0; gi < G; ++gi) {
+    Gpu& D = g_rt.gpus[gi];
+    const int x0 = gi * per < xrows ? gi * per : xrows;
+    const int xn = (x0 + per <= xrows) ? per : xrows - x0;
+    CU(fn_, cudaSetDevice(D.dev));
+    CU(fn_, cascade_match((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, m, n, g, (const float*)D.dict.p, 1,
+                          (uint32_t)x0, (unsigned long long*)D.keys.p, D.ws.p, D.ws.cap, D.stream));
+  }
+  Gpu& R = g_rt.gpus[0];
+  if (G > 1) {
+    for (int gi = 0; gi < G; ++gi) {
+      CU(fn_, cudaSetDevice(g_rt.gpus[gi].dev));
+      CU(fn_, g_rt.gpus[gi].gather.ensure(kbytes * G));
+    }
+    NC(fn_, g_rt.nccl.GroupStart());
+    for (int gi = 0; gi < G; ++gi)
+      NC(fn_, g_rt.nccl.AllGather(g_rt.gpus[gi].keys.p, g_rt.gpus[gi].gather.p, (size_t)2 * yrows, ncclUint64,
+                                  g_rt.nccl.comms[gi], g_rt.gpus[gi].stream));
+    NC(fn_, g_rt.nccl.GroupEnd());
+    CU(fn_, cudaSetDevice(R.dev));
+    CU(fn_, keys_merge((unsigned long long*)R.keys.p, (const unsigned long long*)R.gather.p, G, yrows, R.stream));
+  }
+  CU(fn_, cudaSetDevice(R.dev));
+  const size_t ib = (size_t)yrows * kcols * sizeof(uint64_t), db = (size_t)yrows * kcols * sizeof(float);
+  CU(fn_, R.oidx.ensure(ib));
+  CU(fn_, R.odist.ensure(db));
+  CU(fn_, cudaMemsetAsync(R.oidx.p, 0, ib, R.stream));    // columns >= 2 keep the caller's zeros (Spectavi.cpp:329-334)
+  CU(fn_, cudaMemsetAsync(R.odist.p, 0, db, R.stream));
+  CU(fn_, keys_finalize_f32((const unsigned long long*)R.keys.p, yrows, kcols, (uint64_t*)R.oidx.p, (float*)R.odist.p, R.stream));
+  CU(fn_, cudaMemcpyAsync(idx, R.oidx.p, ib, cudaMemcpyDeviceToHost, R.stream));
+  CU(fn_, cudaMemcpyAsync(dist, R.odist.p, db, cudaMemcpyDeviceToHost, R.stream));
+  for (int gi = 0; gi < G; ++gi) {
+    CU(fn_, cudaSetDevice(g_rt.gpus[gi].dev));
+    CU(fn_, cudaStreamSynchronize(g_rt.gpus[gi].stream));
   }
   cudaSetDevice(prev);
 }

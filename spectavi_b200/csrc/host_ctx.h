@@ -17,6 +17,14 @@ namespace spv {
 int fail(const char* fmt, ...);
 [[noreturn]] void die(const char* fn, const char* fmt, ...);
 
+// The dictionary of the drop-in entry point (the role of generate_hash_dict,
+// CascadingHashNn.h:86-100): n matrices dim x m of N(0,1) draws from std::mt19937
+// in the reference's loop order, seeded with `seed` instead of std::random_device,
+// and -- when quantize -- rounded to multiples of 1/32 in [-127/32, 127/32] so the
+// projection is exact in every arithmetic (cascade.cu header).  out: [n][dim][m].
+void cascade_dictionary(unsigned seed, int dim, int m, int n, bool quantize, float* out);
+unsigned cascade_seed();   // env SPECTAVI_SEED, else a fixed default
+
 class HostCall {
  public:
   explicit HostCall(const char* fn);
@@ -26,6 +34,9 @@ class HostCall {
   // brute-force sum |x-y|^p top-k over float32 / int32 rows (yrows x k out)
   void lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p, uint64_t* idx,
            void* dist);
+  // cascade-of-hashes matcher, float32 rows holding integers in [-128, 127] (yrows x kcols out)
+  void cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
+               uint64_t* idx, float* dist);
 
  private:
   const char* fn_;

@@ -54,6 +54,8 @@ cudaError_t f32_to_u8(const float* din, uint8_t* dout, size_t count, cudaStream_
 cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, int yrows, int dim, int m, int n, int g,
                           const float* ddict, int dict_terms, uint32_t xoffset, unsigned long long* keys, void* ws,
                           size_t ws_bytes, cudaStream_t stream);
+cudaError_t hash_codes(const uint8_t* drows, int rows, int dim, int m, int n, int g, const float* ddict, int dict_terms,
+                       int32_t* codes, unsigned long long* flips, void* ws, size_t ws_bytes, cudaStream_t stream);
 // launch count bookkeeping (bench.py's gpu_launches)
 unsigned long long launches();
 void count_launch(int n = 1);

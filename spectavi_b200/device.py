@@ -95,3 +95,99 @@ def nn_bruteforcel1k2_sharded(x_shard, y, xoffset, group=None):
         dist.all_gather_into_tensor(gathered, keys, group=group)
         keys_merge(keys, gathered)
     return keys_finalize(keys)
+
+
+# ------------------------------------------------------------------ cascade of hashes
+import numpy as _np
+
+clib.spv_f32_to_u8_device.restype = ct.c_int
+clib.spv_f32_to_u8_device.argtypes = [_vp, _vp, ct.c_size_t, _vp]
+clib.spv_cascade_ws_bytes.restype = ct.c_size_t
+clib.spv_cascade_ws_bytes.argtypes = [ct.c_int] * 6
+clib.spv_cascade_device.restype = ct.c_int
+clib.spv_cascade_device.argtypes = [_vp, _vp] + [ct.c_int] * 6 + [_vp, ct.c_int, ct.c_uint32, _vp, _vp, ct.c_size_t, _vp]
+clib.spv_hash_codes_device.restype = ct.c_int
+clib.spv_hash_codes_device.argtypes = [_vp] + [ct.c_int] * 5 + [_vp, ct.c_int, _vp, _vp, _vp, ct.c_size_t, _vp]
+clib.spv_cascade_dictionary.restype = None
+clib.spv_cascade_dictionary.argtypes = [ct.c_uint, ct.c_int, ct.c_int, ct.c_int, ct.c_int, _vp]
+clib.spv_cascade_seed.restype = ct.c_uint
+clib.spv_cascade_seed.argtypes = []
+
+
+def cascade_seed():
+    return int(clib.spv_cascade_seed())
+
+
+def cascade_dictionary(dim, m, n, seed=None, quantize=True):
+    """The hyperplanes nn_cascading_hash uses for these parameters: float32 [n, dim, m] (numpy)."""
+    out = _np.zeros((n, dim, m), _np.float32)
+    clib.spv_cascade_dictionary(cascade_seed() if seed is None else int(seed), dim, m, n, int(bool(quantize)),
+                                out.ctypes.data)
+    return out
+
+
+def f32_to_u8(t):
+    """K0: float32 rows holding integers in [-128, 127] -> uint8 (value + 128)."""
+    assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+    out = torch.empty(t.shape, dtype=torch.uint8, device=t.device)
+    _check(clib.spv_f32_to_u8_device(t.data_ptr(), out.data_ptr(), t.numel(), _stream()), "spv_f32_to_u8_device")
+    return out
+
+
+def _ws(xrows, yrows, dim, m, n, g, device):
+    nbytes = int(clib.spv_cascade_ws_bytes(xrows, yrows, dim, m, n, g))
+    if nbytes == 0:
+        raise ValueError("cascade: unsupported parameters dim=%d m=%d n=%d g=%d" % (dim, m, n, g))
+    return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+
+
+def dict_terms_of(dictionary):
+    """1 when every hyperplane coefficient is exact in bf16, else 3."""
+    d = dictionary if torch.is_tensor(dictionary) else torch.from_numpy(_np.ascontiguousarray(dictionary))
+    return 1 if bool((d.float().bfloat16().float() == d.float()).all()) else 3
+
+
+def hash_codes(rows_u8, dictionary, g=0, dict_terms=None):
+    """K2 alone: (codes int32 [n, rows], flips int64 [n, rows] or None)."""
+    n, dim, m = dictionary.shape
+    assert rows_u8.is_cuda and rows_u8.dtype == torch.uint8 and rows_u8.shape[1] == dim and rows_u8.is_contiguous()
+    rows = rows_u8.shape[0]
+    d = dictionary.to(rows_u8.device, torch.float32).contiguous()
+    ws, nbytes = _ws(rows, rows, dim, m, n, g, rows_u8.device)
+    codes = torch.zeros((n, rows), dtype=torch.int32, device=rows_u8.device)
+    flips = torch.zeros((n, rows), dtype=torch.int64, device=rows_u8.device)
+    terms = dict_terms_of(d) if dict_terms is None else dict_terms
+    _check(clib.spv_hash_codes_device(rows_u8.data_ptr(), rows, dim, m, n, g, d.data_ptr(), terms, codes.data_ptr(),
+                                      flips.data_ptr(), ws.data_ptr(), nbytes, _stream()), "spv_hash_codes_device")
+    return codes, (flips if g > 0 else None)
+
+
+def cascade_fold(x_u8, y_u8, keys, dictionary, g, xoffset=0, dict_terms=None):
+    """K2-K4: fold the cascade-of-hashes top-2 of query rows y_u8 among train rows x_u8 into keys."""
+    n, dim, m = dictionary.shape
+    assert x_u8.dtype == torch.uint8 and y_u8.dtype == torch.uint8 and x_u8.is_contiguous() and y_u8.is_contiguous()
+    assert x_u8.shape[1] == dim and y_u8.shape[1] == dim and keys.shape == (2, y_u8.shape[0])
+    d = dictionary.to(y_u8.device, torch.float32).contiguous()
+    ws, nbytes = _ws(x_u8.shape[0], y_u8.shape[0], dim, m, n, g, y_u8.device)
+    terms = dict_terms_of(d) if dict_terms is None else dict_terms
+    _check(clib.spv_cascade_device(x_u8.data_ptr(), y_u8.data_ptr(), x_u8.shape[0], y_u8.shape[0], dim, m, n, g,
+                                   d.data_ptr(), terms, int(xoffset), keys.data_ptr(), ws.data_ptr(), nbytes, _stream()),
+           "spv_cascade_device")
+    return ws   # keep alive until the stream has consumed it
+
+
+def nn_cascading_hash_sharded(x_shard_u8, y_u8, dictionary, g, xoffset, group=None):
+    """The cascade matcher with the train set sharded over the ranks of ``group``: every rank
+    hashes its shard with the SAME dictionary, probes with all queries, and the per-rank top-2
+    keys are all-gathered over NCCL and merged.  Returns (idx, dist float32)."""
+    import torch.distributed as dist
+    keys = new_keys(y_u8.shape[0], y_u8.device)
+    ws = cascade_fold(x_shard_u8, y_u8, keys, dictionary, g, xoffset)
+    if group is not None or (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+        world = dist.get_world_size(group)
+        gathered = torch.empty((world,) + tuple(keys.shape), dtype=keys.dtype, device=keys.device)
+        dist.all_gather_into_tensor(gathered, keys, group=group)
+        keys_merge(keys, gathered)
+    out = keys_finalize(keys, 2, torch.float32)
+    del ws
+    return out
