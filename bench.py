@@ -229,9 +229,8 @@ def run_b200(args):
     from spectavi_b200 import feature
 
     wname, (xr, yr, dim) = workload_of(args, world)
-    per = (xr + world - 1) // world            # train rows per rank
-    x0 = min(rank * per, xr)
-    xn = min(per, xr - x0)
+    from spectavi_b200.sharding import shard_range
+    x0, xn = shard_range(xr, world, rank)      # train rows of this rank
     hx = torch.from_numpy(host_rows(xn, dim, 11, lo=x0)).pin_memory()
     hy = torch.from_numpy(host_rows(yr, dim, 13)).pin_memory()
     dx, dy = hx.to(device), hy.to(device)
