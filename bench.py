@@ -348,9 +348,12 @@ def run_b200(args):
             sad = [v for k, v in tab.items() if k.startswith("sad4_acc(")][0]
             roof["peak"] = sad["gops"]
             roof["frac"] = achieved / sad["gops"]
-            roof["peak_source"] = ("spv_pipe_peak in this run: VABSDIFF4.U8.ACC %.1f thread-ops/clk/SM, %.0f G ops/s (burst, "
-                                   "CUDA events)" % (sad["ops_per_clk_sm"], sad["gops"]))
-            roof["pipe_table"] = {k: round(v["ops_per_clk_sm"], 2) for k, v in tab.items()}
+            sms = torch.cuda.get_device_properties(local).multi_processor_count
+            mhz = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
+            roof["peak_source"] = ("spv_pipe_peak in this run (pipe_peak.cu): VABSDIFF4.U8.ACC issues %.0f G thread-ops/s on an idle "
+                                   "GPU (burst, CUDA events) = %.1f per clk per SM at %d SMs x %.0f MHz (nominal 64: half-rate ALU pipe)"
+                                   % (sad["gops"], sad["gops"] * 1e3 / (sms * mhz), sms, mhz))
+            roof["pipe_table_gops"] = {k: round(v["gops"], 0) for k, v in tab.items()}
     try:
         prof = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
         roof["traffic"] = prof.get("dram_bytes_per_launch")
