@@ -432,31 +432,49 @@ __global__ void __launch_bounds__(PR_WARPS * 32) probe_rerank_kernel(const PrPar
 
   unsigned long long k1 = KEY_NONE, k2 = KEY_NONE;
 
-  // L1 distance of train row `id` to the query row by the 8 lanes of a group; id < 0: skip
-  auto offer = [&](int id) {
-    uint32_t d = 0;
-    if (id >= 0) {
-      const uint4* xr = reinterpret_cast<const uint4*>(P.xu8 + (size_t)id * P.dim);
+  // L1 distance of up to 4 train rows per 8-lane group (16 per warp) to the query row.
+  // All 4 row gathers are issued before the first is consumed: the kernel is bound by
+  // the latency of random 128-byte row reads, so memory-level parallelism is what counts.
+  // id < 0: nothing to do for that slot (the shuffles still run warp-wide).
+  auto offer4 = [&](const int (&id)[4]) {
+    uint4 v[4];
 #pragma unroll
-      for (int c = 0; c < 4; ++c)
-        if (l8 + 8 * c < nk16) {
-          const uint4 v = __ldg(xr + l8 + 8 * c);
-          d = sad4(v.x, yv[c].x, d); d = sad4(v.y, yv[c].y, d);
-          d = sad4(v.z, yv[c].z, d); d = sad4(v.w, yv[c].w, d);
-        }
-    }
-    d += __shfl_xor_sync(FULL, d, 1);
-    d += __shfl_xor_sync(FULL, d, 2);
-    d += __shfl_xor_sync(FULL, d, 4);
-    if (id >= 0) {
-      const unsigned long long key = ((unsigned long long)d << 32) | (uint32_t)(P.xoffset + (uint32_t)id);
-      if (key < k1) { k2 = k1; k1 = key; }
-      else if (key != k1 && key < k2) k2 = key;
+    for (int u = 0; u < 4; ++u)
+      v[u] = (id[u] >= 0 && l8 < nk16) ? __ldg(reinterpret_cast<const uint4*>(P.xu8 + (size_t)id[u] * P.dim) + l8)
+                                       : yv[0];   // |y - y| = 0
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint32_t d = 0;
+      d = sad4(v[u].x, yv[0].x, d); d = sad4(v[u].y, yv[0].y, d);
+      d = sad4(v[u].z, yv[0].z, d); d = sad4(v[u].w, yv[0].w, d);
+      if (nk16 > 8 && id[u] >= 0) {   // rows wider than 128 B: chunks l8 + 8, l8 + 16, l8 + 24
+        const uint4* xr = reinterpret_cast<const uint4*>(P.xu8 + (size_t)id[u] * P.dim);
+#pragma unroll
+        for (int c = 1; c < 4; ++c)
+          if (l8 + 8 * c < nk16) {
+            const uint4 w = __ldg(xr + l8 + 8 * c);
+            d = sad4(w.x, yv[c].x, d); d = sad4(w.y, yv[c].y, d);
+            d = sad4(w.z, yv[c].z, d); d = sad4(w.w, yv[c].w, d);
+          }
+      }
+      d += __shfl_xor_sync(FULL, d, 1);
+      d += __shfl_xor_sync(FULL, d, 2);
+      d += __shfl_xor_sync(FULL, d, 4);
+      if (id[u] >= 0) {
+        const unsigned long long key = ((unsigned long long)d << 32) | (uint32_t)(P.xoffset + (uint32_t)id[u]);
+        if (key < k1) { k2 = k1; k1 = key; }
+        else if (key != k1 && key < k2) k2 = key;
+      }
     }
   };
   auto drain = [&](int count) {
     __syncwarp();
-    for (int c0 = 0; c0 < count; c0 += 4) offer(c0 + grp < count ? list[c0 + grp] : -1);
+    for (int c0 = 0; c0 < count; c0 += 16) {
+      int id[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) id[u] = (c0 + 4 * u + grp < count) ? list[c0 + 4 * u + grp] : -1;
+      offer4(id);
+    }
     __syncwarp();
   };
 
@@ -504,13 +522,17 @@ __global__ void __launch_bounds__(PR_WARPS * 32) probe_rerank_kernel(const PrPar
         const uint32_t s_start = __shfl_sync(FULL, start, src), s_len = __shfl_sync(FULL, len, src);
         const uint32_t s_code = __shfl_sync(FULL, code, src);
         const int s_t = __shfl_sync(FULL, t, src);
-        for (uint32_t c0 = 0; c0 < s_len; c0 += 4) {
-          int id = -1;
-          if (c0 + grp < s_len) {
-            id = P.ids[s_start + c0 + grp];
-            if (verify && (uint32_t)P.xcodes[(size_t)s_t * P.xrows + id] != s_code) id = -1;
+        for (uint32_t c0 = 0; c0 < s_len; c0 += 16) {
+          int id[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            id[u] = -1;
+            if (c0 + 4 * u + grp < s_len) {
+              id[u] = P.ids[s_start + c0 + 4 * u + grp];
+              if (verify && (uint32_t)P.xcodes[(size_t)s_t * P.xrows + id[u]] != s_code) id[u] = -1;
+            }
           }
-          offer(id);
+          offer4(id);
         }
       }
     }
