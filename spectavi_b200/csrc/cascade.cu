@@ -413,7 +413,7 @@ __device__ __forceinline__ void top2_merge(unsigned long long& a1, unsigned long
   a2 = s;
 }
 
-__global__ void __launch_bounds__(PR_WARPS * 32) probe_rerank_kernel(const PrParams P) {
+__global__ void __launch_bounds__(PR_WARPS * 32, 5) probe_rerank_kernel(const PrParams P) {
   __shared__ int32_t lists[PR_WARPS][PR_LCAP];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 3, l8 = lane & 7;
   const int r = blockIdx.x * PR_WARPS + warp;
