@@ -76,6 +76,19 @@ void nn_bruteforcei(const int *x, const int *y, int xrows, int yrows, int dim, i
 void nn_cascading_hash(const float *x, const float *y, int xrows, int yrows, int dim, int k, int hash_bit_rate,
                        int num_hash_tables, int num_candidate_neighbours, NdArray *outidx, NdArray *outdist);
 
+/* ---- Part 1b: the step after the matcher, same calling convention.
+ * The reference applies the ratio test in numpy (example/ex01_essential_estimation.py:102-105:
+ * ratio = d2 / float64(d1); pass = ratio >= min_ratio; matches = (idx0[pass], arange(yrows)[pass]))
+ * on the yrows x 2 arrays the matcher returned.  These entry points run the matcher, the
+ * ratio test and the compaction on the GPU and return only the surviving pairs:
+ * outmatches count x 2 uint64, column 0 = train index, column 1 = query row, query order kept.
+ * Identical to applying the numpy lines above to nn_bruteforcel1k2's / nn_cascading_hash's output. */
+void spv_match_bruteforcel1k2(const uint8_t *x, const uint8_t *y, int xrows, int yrows, int dim, double min_ratio,
+                              NdArray *outmatches);
+void spv_match_cascading_hash(const float *x, const float *y, int xrows, int yrows, int dim, int hash_bit_rate,
+                              int num_hash_tables, int num_candidate_neighbours, double min_ratio,
+                              NdArray *outmatches);
+
 /* ============================ Part 2: device-resident API (device pointers)
  * Results live in a KEY buffer: uint64 keys[2][yrows], key = dist << 32 | idx,
  * all-ones = none; unsigned order of keys == the reference's (dist, idx) rule. */
@@ -93,6 +106,13 @@ int spv_keys_merge(uint64_t *dkeys, const uint64_t *dsrc, int nsrc, int yrows, v
  * dist yrows x kcols int32 / float32 */
 int spv_keys_finalize_i32(const uint64_t *dkeys, int yrows, int kcols, uint64_t *didx, int32_t *ddist, void *stream);
 int spv_keys_finalize_f32(const uint64_t *dkeys, int yrows, int kcols, uint64_t *didx, float *ddist, void *stream);
+
+/* K6: ratio test + compaction on a key buffer.  dist_is_f32: divide as float32 / float64 (the
+ * cascade matcher's output dtype, sentinel 2147483648.0f) instead of int32 / float64.  dmask
+ * (nullable): yrows bytes, 1 = pass.  dmatches: room for yrows x 2 uint64; dcount: one uint32. */
+size_t spv_ratio_ws_bytes(int yrows);
+int spv_ratio_matches_device(const uint64_t *dkeys, int yrows, double min_ratio, int dist_is_f32, uint8_t *dmask,
+                             uint64_t *dmatches, uint32_t *dcount, void *dws, size_t ws_bytes, void *stream);
 
 /* K0: (uint8)((int)v + 128), the cast of CascadingHashNn.h:236-239 (count % 4 == 0) */
 int spv_f32_to_u8_device(const float *din, uint8_t *dout, size_t count, void *stream);

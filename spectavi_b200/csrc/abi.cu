@@ -95,6 +95,16 @@ int spv_keys_finalize_f32(const uint64_t* dkeys, int yrows, int kcols, uint64_t*
   return 0;
 }
 
+size_t spv_ratio_ws_bytes(int yrows) { return ratio_ws_bytes(yrows); }
+
+int spv_ratio_matches_device(const uint64_t* dkeys, int yrows, double min_ratio, int dist_is_f32, uint8_t* dmask,
+                             uint64_t* dmatches, uint32_t* dcount, void* dws, size_t ws_bytes, void* stream) {
+  if (yrows < 0) return fail("negative row count");
+  CU_OR_FAIL(ratio_matches(reinterpret_cast<const unsigned long long*>(dkeys), yrows, min_ratio, dist_is_f32 != 0, dmask,
+                           dmatches, dcount, dws, ws_bytes, (cudaStream_t)stream));
+  return 0;
+}
+
 int spv_f32_to_u8_device(const float* din, uint8_t* dout, size_t count, void* stream) {
   CU_OR_FAIL(f32_to_u8(din, dout, count, (cudaStream_t)stream));
   return 0;
@@ -143,6 +153,36 @@ void nn_bruteforcel1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows,
   HostCall hc("nn_bruteforcel1k2");
   hc.l1k2(x, y, xrows, yrows, dim, reinterpret_cast<uint64_t*>(outidx->m_data),
           reinterpret_cast<int32_t*>(outdist->m_data));
+}
+
+// ---- Part 1b: matcher + ratio test + compaction (example/ex01_essential_estimation.py:102-105)
+static MatchSink sink_for(NdArray* outmatches, double min_ratio) {
+  return MatchSink{min_ratio, [outmatches](uint64_t count) {
+                     out_alloc(outmatches, count, 2);   // sized after the device count is known
+                     return reinterpret_cast<uint64_t*>(outmatches->m_data);
+                   }};
+}
+
+void spv_match_bruteforcel1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, double min_ratio,
+                              NdArray* outmatches) {
+  const char* fn = "spv_match_bruteforcel1k2";
+  if (dim % 16 != 0) die(fn, "data dimension (%d) must be a multiple of 16", dim);
+  if (xrows < 0 || yrows < 0 || dim <= 0) die(fn, "bad shape %d x %d x %d", xrows, yrows, dim);
+  if (yrows == 0) { out_alloc(outmatches, 0, 2); return; }
+  const MatchSink ms = sink_for(outmatches, min_ratio);
+  HostCall hc(fn);
+  hc.l1k2(x, y, xrows, yrows, dim, nullptr, nullptr, &ms);
+}
+
+void spv_match_cascading_hash(const float* x, const float* y, int xrows, int yrows, int dim, int hash_bit_rate,
+                              int num_hash_tables, int num_candidate_neighbours, double min_ratio, NdArray* outmatches) {
+  const char* fn = "spv_match_cascading_hash";
+  if (xrows < 0 || yrows < 0 || dim <= 0) die(fn, "bad shape %d x %d x %d", xrows, yrows, dim);
+  if (dim % 16 != 0) die(fn, "data dimension (%d) must be a multiple of 16", dim);
+  if (yrows == 0) { out_alloc(outmatches, 0, 2); return; }
+  const MatchSink ms = sink_for(outmatches, min_ratio);
+  HostCall hc(fn);
+  hc.cascade(x, y, xrows, yrows, dim, 2, hash_bit_rate, num_hash_tables, num_candidate_neighbours, nullptr, nullptr, &ms);
 }
 
 static void lp_entry(const char* fn, const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k,

@@ -383,8 +383,9 @@ __global__ void bucket_scatter_kernel(const int32_t* __restrict__ codes, size_t 
 }
 
 // ---------------------------------------------------------------- K4
-constexpr int PR_WARPS = 8;      // query rows per CTA (one warp each)
-constexpr int PR_LCAP = 256;     // candidate ids staged per warp before a distance pass
+constexpr int PR_WARPS = 4;      // warps per CTA
+constexpr int PR_QPW = 4;        // query rows per warp (one per 8-lane group)
+constexpr int PR_LCAP = 128;     // candidate ids staged per query before a distance pass (multiple of 8)
 
 struct PrParams {
   const uint8_t* xu8;            // [xrows][dim]
@@ -413,139 +414,164 @@ __device__ __forceinline__ void top2_merge(unsigned long long& a1, unsigned long
   a2 = s;
 }
 
-__global__ void __launch_bounds__(PR_WARPS * 32, 5) probe_rerank_kernel(const PrParams P) {
-  __shared__ int32_t lists[PR_WARPS][PR_LCAP];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 3, l8 = lane & 7;
-  const int r = blockIdx.x * PR_WARPS + warp;
-  if (r >= P.yrows) return;   // whole warp
+// One 8-lane group per query row, four queries per warp, control flow warp-uniform.
+// NCH = 16-byte chunks of a row per lane = ceil(dim / 128).  Per group:
+//  (1) lanes enumerate the probe codes 8 at a time and read their bucket ranges;
+//  (2) the ranges are FLATTENED: candidate slot f of the chunk belongs to the probe found by a
+//      3-step shuffle search in the group's inclusive prefix of range lengths, so all id loads
+//      of a chunk are independent and issued together (a lane walking its own bucket would
+//      serialise one memory latency per candidate);
+//  (3) ids are staged in shared memory and drained 8 at a time: the 8 row gathers of a step
+//      (8 lanes x 16 B = one 128-byte line each) are all issued before the first is consumed,
+//      each lane folds 4 VABSDIFF4 per row, and a transposed butterfly (7 shuffles for 8 rows
+//      instead of 24) leaves candidate l8's distance in lane l8, which makes ONE branch-free
+//      top-2 update per lane and step.
+// The kernel is bound by the latency of dependent random reads (codes -> bucket range -> ids ->
+// rows), so what counts is queries in flight per SM: 4 per warp x 32 warps at 64 registers.
+template <int NCH>
+__global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_kernel(const PrParams P) {
+  __shared__ __align__(16) int32_t lists[PR_WARPS][PR_QPW][PR_LCAP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = lane >> 3, l8 = lane & 7;
+  const long long first = ((long long)blockIdx.x * PR_WARPS + warp) * PR_QPW;
+  if (first >= P.yrows) return;   // whole warp
+  const bool live = first + q < P.yrows;
+  const int r = live ? (int)(first + q) : P.yrows - 1;   // a dead group shadows the last row and offers nothing
   const unsigned FULL = 0xFFFFFFFFu;
   const int nk16 = P.dim / 16;
   const uint32_t mask = (P.mb >= 32) ? 0xFFFFFFFFu : ((1u << P.mb) - 1u);
   const bool verify = P.m > P.mb;
-  int32_t* list = lists[warp];
+  int32_t* list = lists[warp][q];
 
   // this lane's 16-byte slices of the query row: chunks l8, l8 + 8, ...
-  uint4 yv[4];
+  uint4 yv[NCH];
   const uint4* yrow = reinterpret_cast<const uint4*>(P.yu8 + (size_t)r * P.dim);
 #pragma unroll
-  for (int c = 0; c < 4; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
+  for (int c = 0; c < NCH; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
 
-  unsigned long long k1 = KEY_NONE, k2 = KEY_NONE;
+  unsigned long long k1 = KEY_NONE, k2 = KEY_NONE;   // this lane's running top-2 (distinct keys)
+  const bool b2 = (l8 & 4) != 0, b1 = (l8 & 2) != 0, b0 = (l8 & 1) != 0;
+  int listn = 0;                                     // ids staged for this group's query
 
-  // L1 distance of up to 4 train rows per 8-lane group (16 per warp) to the query row.
-  // All 4 row gathers are issued before the first is consumed: the kernel is bound by
-  // the latency of random 128-byte row reads, so memory-level parallelism is what counts.
-  // id < 0: nothing to do for that slot (the shuffles still run warp-wide).
-  auto offer4 = [&](const int (&id)[4]) {
-    uint4 v[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-      v[u] = (id[u] >= 0 && l8 < nk16) ? __ldg(reinterpret_cast<const uint4*>(P.xu8 + (size_t)id[u] * P.dim) + l8)
-                                       : yv[0];   // |y - y| = 0
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      uint32_t d = 0;
-      d = sad4(v[u].x, yv[0].x, d); d = sad4(v[u].y, yv[0].y, d);
-      d = sad4(v[u].z, yv[0].z, d); d = sad4(v[u].w, yv[0].w, d);
-      if (nk16 > 8 && id[u] >= 0) {   // rows wider than 128 B: chunks l8 + 8, l8 + 16, l8 + 24
-        const uint4* xr = reinterpret_cast<const uint4*>(P.xu8 + (size_t)id[u] * P.dim);
-#pragma unroll
-        for (int c = 1; c < 4; ++c)
-          if (l8 + 8 * c < nk16) {
-            const uint4 w = __ldg(xr + l8 + 8 * c);
-            d = sad4(w.x, yv[c].x, d); d = sad4(w.y, yv[c].y, d);
-            d = sad4(w.z, yv[c].z, d); d = sad4(w.w, yv[c].w, d);
-          }
-      }
-      d += __shfl_xor_sync(FULL, d, 1);
-      d += __shfl_xor_sync(FULL, d, 2);
-      d += __shfl_xor_sync(FULL, d, 4);
-      if (id[u] >= 0) {
-        const unsigned long long key = ((unsigned long long)d << 32) | (uint32_t)(P.xoffset + (uint32_t)id[u]);
-        if (key < k1) { k2 = k1; k1 = key; }
-        else if (key != k1 && key < k2) k2 = key;
-      }
-    }
-  };
-  auto drain = [&](int count) {
+  auto drain = [&]() {
+    if ((listn & 7) && l8 >= (listn & 7)) list[(listn & ~7) + l8] = -1;   // pad the last step
     __syncwarp();
-    for (int c0 = 0; c0 < count; c0 += 16) {
-      int id[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) id[u] = (c0 + 4 * u + grp < count) ? list[c0 + 4 * u + grp] : -1;
-      offer4(id);
-    }
-    __syncwarp();
-  };
-
-  const int P_total = P.n << P.nb;   // probe codes of this query: n tables x 2^nb settings
-  int listn = 0;
-  for (int p0 = 0; p0 < P_total; p0 += 32) {
-    const int p = p0 + lane;
-    uint32_t start = 0, len = 0;
-    int t = 0;
-    uint32_t code = 0;
-    if (p < P_total) {
-      t = p >> P.nb;
-      const uint32_t combo = (uint32_t)p & ((1u << P.nb) - 1u);
-      code = (uint32_t)P.ycodes[(size_t)t * P.yrows + r];
-      const unsigned long long fl = P.yflips[(size_t)t * P.yrows + r];
-      for (int q = 0; q < P.nb; ++q) {   // generate_y_candidate_hashcodes :170-179
-        const uint32_t bit = (uint32_t)(fl >> (5 * q)) & 31u;
-        code = (code & ~(1u << bit)) | (((combo >> q) & 1u) << bit);
+    const int nmax = __reduce_max_sync(FULL, listn);
+    for (int c0 = 0; c0 < nmax; c0 += 8) {
+      int4 ia = make_int4(-1, -1, -1, -1), ib = ia;
+      int own = -1;                       // the candidate whose distance ends up in this lane
+      if (c0 < listn) {
+        ia = *reinterpret_cast<const int4*>(list + c0);
+        ib = *reinterpret_cast<const int4*>(list + c0 + 4);
+        own = list[c0 + l8];
       }
-      const size_t b = ((size_t)t << P.mb) + (code & mask);
-      const uint32_t end = P.cursor[b];
-      start = b ? P.cursor[b - 1] : 0u;
-      len = end - start;
-    }
-    // exclusive prefix of len over the warp
-    uint32_t inc = len;
+      const int id[8] = {ia.x, ia.y, ia.z, ia.w, ib.x, ib.y, ib.z, ib.w};
+      uint32_t d[8];
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t o = __shfl_up_sync(FULL, inc, d);
-      if (lane >= d) inc += o;
-    }
-    const uint32_t T = __shfl_sync(FULL, inc, 31), off = inc - len;
-    if (T == 0) continue;
-    if (listn + (int)T > PR_LCAP) { drain(listn); listn = 0; }
-    if ((int)T <= PR_LCAP) {
-      for (uint32_t i = 0; i < len; ++i) {
-        int id = P.ids[start + i];
-        if (verify && (uint32_t)P.xcodes[(size_t)t * P.xrows + id] != code) id = -1;
-        list[listn + off + i] = id;
-      }
-      listn += (int)T;
-    } else {
-      // very full buckets: take the lanes' ranges one after the other, straight from global memory
-      for (int src = 0; src < 32; ++src) {
-        const uint32_t s_start = __shfl_sync(FULL, start, src), s_len = __shfl_sync(FULL, len, src);
-        const uint32_t s_code = __shfl_sync(FULL, code, src);
-        const int s_t = __shfl_sync(FULL, t, src);
-        for (uint32_t c0 = 0; c0 < s_len; c0 += 16) {
-          int id[4];
+      for (int u = 0; u < 8; ++u) d[u] = 0;
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            id[u] = -1;
-            if (c0 + 4 * u + grp < s_len) {
-              id[u] = P.ids[s_start + c0 + 4 * u + grp];
-              if (verify && (uint32_t)P.xcodes[(size_t)s_t * P.xrows + id[u]] != s_code) id[u] = -1;
-            }
-          }
-          offer4(id);
+      for (int c = 0; c < NCH; ++c) {
+        uint4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          v[u] = (id[u] >= 0 && l8 + 8 * c < nk16)
+                     ? __ldg(reinterpret_cast<const uint4*>(P.xu8 + (size_t)id[u] * P.dim) + l8 + 8 * c)
+                     : yv[c];   // |y - y| = 0
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          d[u] = sad4(v[u].x, yv[c].x, d[u]); d[u] = sad4(v[u].y, yv[c].y, d[u]);
+          d[u] = sad4(v[u].z, yv[c].z, d[u]); d[u] = sad4(v[u].w, yv[c].w, d[u]);
         }
       }
+      // transposed butterfly over the 8 lanes of the group: lane l8 ends with sum_lanes d[l8]
+      uint32_t e[4], f[2];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t send = b2 ? d[u] : d[u + 4], keep = b2 ? d[u + 4] : d[u];
+        e[u] = keep + __shfl_xor_sync(FULL, send, 4);
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const uint32_t send = b1 ? e[u] : e[u + 2], keep = b1 ? e[u + 2] : e[u];
+        f[u] = keep + __shfl_xor_sync(FULL, send, 2);
+      }
+      const uint32_t send = b0 ? f[0] : f[1], keep = b0 ? f[1] : f[0];
+      const uint32_t dist = keep + __shfl_xor_sync(FULL, send, 1);
+      // branch-free insert of one key into the distinct top-2
+      const unsigned long long key =
+          own >= 0 ? (((unsigned long long)dist << 32) | (uint32_t)(P.xoffset + (uint32_t)own)) : KEY_NONE;
+      const unsigned long long lo = key < k1 ? key : k1, hi = key < k1 ? k1 : key;
+      k2 = (hi == lo) ? k2 : (hi < k2 ? hi : k2);
+      k1 = lo;
+    }
+    __syncwarp();
+    listn = 0;
+  };
+
+  const int P_total = P.n << P.nb;   // probe codes of a query: n tables x 2^nb settings
+  for (int p0 = 0; p0 < P_total; p0 += 8) {
+    const int p = p0 + l8;
+    uint32_t start = 0, len = 0, code = 0;
+    int t = 0;
+    if (live && p < P_total) {
+      t = p >> P.nb;
+      const uint32_t combo = (uint32_t)p & ((1u << P.nb) - 1u);
+      code = (uint32_t)__ldg(P.ycodes + (size_t)t * P.yrows + r);
+      const unsigned long long fl = __ldg(P.yflips + (size_t)t * P.yrows + r);
+      for (int b = 0; b < P.nb; ++b) {   // generate_y_candidate_hashcodes :170-179
+        const uint32_t bit = (uint32_t)(fl >> (5 * b)) & 31u;
+        code = (code & ~(1u << bit)) | (((combo >> b) & 1u) << bit);
+      }
+      const size_t bk = ((size_t)t << P.mb) + (code & mask);
+      const uint32_t end = __ldg(P.cursor + bk);
+      start = bk ? __ldg(P.cursor + bk - 1) : 0u;
+      len = end - start;
+    }
+    // inclusive prefix of len over the 8 lanes of the group
+    uint32_t inc = len;
+#pragma unroll
+    for (int d = 1; d < 8; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(FULL, inc, d, 8);
+      if (l8 >= d) inc += o;
+    }
+    const uint32_t T = __shfl_sync(FULL, inc, 7, 8), excl = inc - len;
+    uint32_t done = 0;
+    while (__any_sync(FULL, done < T)) {
+      if (__any_sync(FULL, done < T && listn == PR_LCAP)) drain();   // some group is full: all groups drain
+      const uint32_t room = (uint32_t)(PR_LCAP - listn), take = (T - done) < room ? (T - done) : room;
+      const uint32_t takemax = __reduce_max_sync(FULL, take);
+      for (uint32_t f0 = 0; f0 < takemax; f0 += 8) {
+        const uint32_t f = done + f0 + l8;
+        // owner probe of flat slot f: the number of group lanes whose inclusive prefix is <= f
+        int pos = 0;
+#pragma unroll
+        for (int step = 4; step >= 1; step >>= 1) {
+          const uint32_t v = __shfl_sync(FULL, inc, pos + step - 1, 8);
+          pos += (v <= f) ? step : 0;
+        }
+        pos = pos > 7 ? 7 : pos;
+        const uint32_t s_start = __shfl_sync(FULL, start, pos, 8), s_excl = __shfl_sync(FULL, excl, pos, 8);
+        uint32_t s_code = 0;
+        int s_t = 0;
+        if (verify) { s_code = __shfl_sync(FULL, code, pos, 8); s_t = __shfl_sync(FULL, t, pos, 8); }
+        if (f0 + l8 < take) {
+          int id = __ldg(P.ids + s_start + (f - s_excl));
+          if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = -1;
+          list[listn + f0 + l8] = id;
+        }
+      }
+      listn += (int)take;
+      done += take;
     }
   }
-  drain(listn);
+  if (__any_sync(FULL, listn != 0)) drain();
 
-  // the four lane groups hold disjoint-or-duplicate candidate subsets
+  // every lane of the group holds the top-2 of a disjoint-or-duplicate candidate subset
 #pragma unroll
-  for (int d = 8; d <= 16; d <<= 1) {
+  for (int d = 1; d <= 4; d <<= 1) {
     const unsigned long long o1 = __shfl_xor_sync(FULL, k1, d), o2 = __shfl_xor_sync(FULL, k2, d);
     top2_merge(k1, k2, o1, o2);
   }
-  if (lane == 0) {   // fold into what other train shards / launches left there
+  if (l8 == 0 && live) {   // fold into what other train shards / launches left there
     unsigned long long e1 = P.keys[r], e2 = P.keys[(size_t)P.yrows + r];
     top2_merge(e1, e2, k1, k2);
     P.keys[r] = e1;
@@ -703,7 +729,13 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
   pr.xu8 = dxu8; pr.yu8 = dyu8; pr.xcodes = xcodes; pr.ycodes = ycodes; pr.yflips = yflips; pr.cursor = cursor; pr.ids = ids;
   pr.xrows = xrows; pr.yrows = yrows; pr.dim = dim; pr.n = n; pr.m = m; pr.mb = pl.mb; pr.nb = pl.nb; pr.xoffset = xoffset;
   pr.keys = keys;
-  probe_rerank_kernel<<<(yrows + PR_WARPS - 1) / PR_WARPS, PR_WARPS * 32, 0, stream>>>(pr);
+  const unsigned prgrid = (unsigned)((yrows + PR_WARPS * PR_QPW - 1) / (PR_WARPS * PR_QPW));
+  switch ((dim + 127) / 128) {
+    case 1: probe_rerank_kernel<1><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
+    case 2: probe_rerank_kernel<2><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
+    case 3: probe_rerank_kernel<3><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
+    default: probe_rerank_kernel<4><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
+  }
   count_launch();
   return cudaGetLastError();
 }

@@ -33,7 +33,7 @@ struct Buf {
 struct Gpu {
   int dev = -1;
   cudaStream_t stream = nullptr;
-  Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws;
+  Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws, rws;
 };
 
 struct Nccl {
@@ -115,7 +115,33 @@ void init_runtime(const char* fn) {
 HostCall::HostCall(const char* fn) : fn_(fn), lock_(g_mu) { init_runtime(fn); }
 HostCall::~HostCall() {}
 
-void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist) {
+// K6 on the merged key buffer of GPU 0: ratio test + compaction on the device, then only
+// count x 16 bytes come back (instead of yrows x 2 x 12)
+void HostCall::deliver_matches(const MatchSink& ms, int yrows, bool dist_f32) {
+  Gpu& R = g_rt.gpus[0];
+  CU(fn_, cudaSetDevice(R.dev));
+  const size_t wsb = ratio_ws_bytes(yrows);
+  CU(fn_, R.rws.ensure(wsb + 16));
+  CU(fn_, R.oidx.ensure((size_t)yrows * 2 * sizeof(uint64_t)));
+  unsigned* dcount = reinterpret_cast<unsigned*>(static_cast<char*>(R.rws.p) + ((wsb + 7) / 8) * 8);
+  CU(fn_, ratio_matches((const unsigned long long*)R.keys.p, yrows, ms.min_ratio, dist_f32, nullptr, (uint64_t*)R.oidx.p,
+                        dcount, R.rws.p, wsb, R.stream));
+  unsigned count = 0;
+  CU(fn_, cudaMemcpyAsync(&count, dcount, sizeof(count), cudaMemcpyDeviceToHost, R.stream));
+  for (size_t g = 0; g < g_rt.gpus.size(); ++g) {
+    CU(fn_, cudaSetDevice(g_rt.gpus[g].dev));
+    CU(fn_, cudaStreamSynchronize(g_rt.gpus[g].stream));
+  }
+  CU(fn_, cudaSetDevice(R.dev));
+  uint64_t* out = ms.alloc(count);
+  if (count) {
+    CU(fn_, cudaMemcpyAsync(out, R.oidx.p, (size_t)count * 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, R.stream));
+    CU(fn_, cudaStreamSynchronize(R.stream));
+  }
+}
+
+void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist,
+                    const MatchSink* ms) {
   const int G = (int)g_rt.gpus.size();
   const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
   const int per = (xrows + G - 1) / G;   // train rows per GPU
@@ -167,6 +193,11 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
     CU(fn_, cudaSetDevice(R.dev));
     CU(fn_, keys_merge((unsigned long long*)R.keys.p, (const unsigned long long*)R.gather.p, G, yrows, R.stream));
   }
+  if (ms) {
+    deliver_matches(*ms, yrows, false);
+    cudaSetDevice(prev);
+    return;
+  }
   CU(fn_, cudaSetDevice(R.dev));
   CU(fn_, R.oidx.ensure((size_t)yrows * 2 * sizeof(uint64_t)));
   CU(fn_, R.odist.ensure((size_t)yrows * 2 * sizeof(int32_t)));
@@ -203,7 +234,7 @@ unsigned cascade_seed() {
 }
 
 void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
-                       uint64_t* idx, float* dist) {
+                       uint64_t* idx, float* dist, const MatchSink* ms) {
   const int G = (int)g_rt.gpus.size();
   const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
   const int per = (xrows + G - 1) / G;   // train rows per GPU, as for brute force
@@ -264,6 +295,11 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
     NC(fn_, g_rt.nccl.GroupEnd());
     CU(fn_, cudaSetDevice(R.dev));
     CU(fn_, keys_merge((unsigned long long*)R.keys.p, (const unsigned long long*)R.gather.p, G, yrows, R.stream));
+  }
+  if (ms) {
+    deliver_matches(*ms, yrows, true);
+    cudaSetDevice(prev);
+    return;
   }
   CU(fn_, cudaSetDevice(R.dev));
   const size_t ib = (size_t)yrows * kcols * sizeof(uint64_t), db = (size_t)yrows * kcols * sizeof(float);

@@ -10,6 +10,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <functional>
 #include <mutex>
 
 namespace spv {
@@ -25,20 +26,30 @@ int fail(const char* fmt, ...);
 void cascade_dictionary(unsigned seed, int dim, int m, int n, bool quantize, float* out);
 unsigned cascade_seed();   // env SPECTAVI_SEED, else a fixed default
 
+// Asks for the ratio-tested, compacted match list (K6) instead of the yrows x k arrays: alloc(count)
+// must return host memory for count x 2 uint64 (called once, from the calling thread).
+struct MatchSink {
+  double min_ratio;
+  std::function<uint64_t*(uint64_t)> alloc;
+};
+
 class HostCall {
  public:
   explicit HostCall(const char* fn);
   ~HostCall();
   // brute-force L1 k=2, host in / host out (reference layout: yrows x 2)
-  void l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist);
+  // (with a MatchSink: idx/dist are ignored and the surviving (train idx, query row) pairs are delivered)
+  void l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist,
+            const MatchSink* ms = nullptr);
   // brute-force sum |x-y|^p top-k over float32 / int32 rows (yrows x k out)
   void lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p, uint64_t* idx,
            void* dist);
   // cascade-of-hashes matcher, float32 rows holding integers in [-128, 127] (yrows x kcols out)
   void cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
-               uint64_t* idx, float* dist);
+               uint64_t* idx, float* dist, const MatchSink* ms = nullptr);
 
  private:
+  void deliver_matches(const MatchSink& ms, int yrows, bool dist_f32);   // K6 on GPU 0's merged keys
   const char* fn_;
   std::unique_lock<std::mutex> lock_;
 };

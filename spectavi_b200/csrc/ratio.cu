@@ -21,7 +21,9 @@ namespace {
 constexpr int RT_THREADS = 256;
 
 __device__ __forceinline__ bool ratio_pass(unsigned long long k0, unsigned long long k1, double min_ratio, bool dist_f32) {
-  const int d0 = (int)(unsigned)(k0 >> 32), d1 = (int)(unsigned)(k1 >> 32);
+  // "no neighbour" is the all-ones key; the reference's arrays hold INT_MAX there (BruteForceNnL1K2.h:99-103)
+  const int d0 = k0 == KEY_NONE ? 0x7FFFFFFF : (int)(unsigned)(k0 >> 32);
+  const int d1 = k1 == KEY_NONE ? 0x7FFFFFFF : (int)(unsigned)(k1 >> 32);
   // int32 / float64 (numpy promotes the int32 numerator), or float32 / float64
   const double den = dist_f32 ? (double)(float)d0 : (double)d0;
   const double num = dist_f32 ? (double)(float)d1 : (double)d1;

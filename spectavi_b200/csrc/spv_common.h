@@ -56,6 +56,12 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
                           size_t ws_bytes, cudaStream_t stream);
 cudaError_t hash_codes(const uint8_t* drows, int rows, int dim, int m, int n, int g, const float* ddict, int dict_terms,
                        int32_t* codes, unsigned long long* flips, void* ws, size_t ws_bytes, cudaStream_t stream);
+// ---- ratio.cu : K6, ratio test + order-preserving compaction of the surviving matches
+// (example/ex01_essential_estimation.py:102-105).  matches: [count][2] uint64 (train idx, query row),
+// count: one uint32; mask (nullable): yrows bytes; ws: ratio_ws_bytes(yrows) scratch.
+size_t ratio_ws_bytes(int yrows);
+cudaError_t ratio_matches(const unsigned long long* keys, int yrows, double min_ratio, bool dist_f32, unsigned char* mask,
+                          uint64_t* matches, unsigned* count, void* ws, size_t ws_bytes, cudaStream_t stream);
 // launch count bookkeeping (bench.py's gpu_launches)
 unsigned long long launches();
 void count_launch(int n = 1);

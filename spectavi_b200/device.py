@@ -80,6 +80,30 @@ def keys_finalize(keys, kcols=2, dist_dtype=torch.int32):
     return idx, dist
 
 
+clib.spv_ratio_ws_bytes.restype = ct.c_size_t
+clib.spv_ratio_ws_bytes.argtypes = [ct.c_int]
+clib.spv_ratio_matches_device.restype = ct.c_int
+clib.spv_ratio_matches_device.argtypes = [_vp, ct.c_int, ct.c_double, ct.c_int, _vp, _vp, _vp, _vp, ct.c_size_t, _vp]
+
+
+def ratio_matches(keys, min_ratio=1.75, dist_f32=False, want_mask=False):
+    """K6: ratio test (second / float64(first) >= min_ratio, example/ex01:102-103) and
+    order-preserving compaction on a key buffer.  Returns ``matches`` int64 [count, 2]
+    (train idx, query row) -- one device->host read of the count -- and, with
+    ``want_mask``, the uint8 pass mask [yrows]."""
+    yrows = keys.shape[1]
+    nbytes = int(clib.spv_ratio_ws_bytes(yrows))
+    ws = torch.empty(nbytes + 8, dtype=torch.uint8, device=keys.device)
+    count = torch.zeros(1, dtype=torch.int32, device=keys.device)
+    matches = torch.empty((yrows, 2), dtype=torch.int64, device=keys.device)
+    mask = torch.empty(yrows, dtype=torch.uint8, device=keys.device) if want_mask else None
+    _check(clib.spv_ratio_matches_device(keys.data_ptr(), yrows, float(min_ratio), int(bool(dist_f32)),
+                                         mask.data_ptr() if want_mask else None, matches.data_ptr(), count.data_ptr(),
+                                         ws.data_ptr(), nbytes, _stream()), "spv_ratio_matches_device")
+    out = matches[:int(count.item())]
+    return (out, mask) if want_mask else out
+
+
 def nn_bruteforcel1k2_sharded(x_shard, y, xoffset, group=None):
     """Brute-force L1 k=2 with the train set sharded over the ranks of ``group``
     (SURVEY.md 8e): every rank folds its shard, the key buffers are

@@ -45,6 +45,21 @@ _nn_cascading_hash.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
                                ct.POINTER(NdArray), ct.POINTER(NdArray)]
 
 
+_match_l1k2 = clib.spv_match_bruteforcel1k2
+_match_l1k2.restype = None
+_match_l1k2.argtypes = [ndpointer(ct.c_ubyte, flags="C_CONTIGUOUS"),
+                        ndpointer(ct.c_ubyte, flags="C_CONTIGUOUS"),
+                        ct.c_int, ct.c_int, ct.c_int, ct.c_double,
+                        ct.POINTER(NdArray)]
+
+_match_cashash = clib.spv_match_cascading_hash
+_match_cashash.restype = None
+_match_cashash.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                           ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                           ct.c_int, ct.c_int, ct.c_int, ct.c_int, ct.c_int,
+                           ct.c_int, ct.c_double, ct.POINTER(NdArray)]
+
+
 def nn_bruteforce(x, y, p=.5, mu=0., k=2, use_int=False):
     """k nearest rows of ``x`` for every row of ``y`` under sum |d|^p
     (reference feature.py:246-289).  Returns ``(idx uint64, dist)`` of shape
@@ -128,3 +143,40 @@ def ratio_test(nn_dist, min_ratio=1.75):
     with np.errstate(divide='ignore', invalid='ignore'):
         ratio = nn_dist[:, 1] / nn_dist[:, 0].astype('float64')
     return ratio >= min_ratio
+
+
+def _split_matches(out):
+    # not NdArray.asarray(): its squeeze() (cndarray/ndarray.py:113-122) would drop the pair axis of a single match
+    m = out.arr.view('uint64').reshape(-1, 2)
+    return m[:, 0].copy(), m[:, 1].copy()
+
+
+def match_bruteforcel1k2(x, y, min_ratio=1.75):
+    """Brute-force L1 k=2 match + ratio test + compaction on the GPU: what
+    example/ex01_essential_estimation.py:95-105 computes with
+    ``nn_bruteforcel1k2`` followed by the numpy ratio test, returned as
+    ``(idx_x, idx_y)`` -- ``idx0[pass_idx]`` and ``arange(yrows)[pass_idx]``."""
+    xrows, xdim = x.shape
+    yrows, ydim = y.shape
+    assert ydim == xdim
+    out = NdArray(dtype='uint64')
+    _match_l1k2(x, y, xrows, yrows, xdim, float(min_ratio), out)
+    return _split_matches(out)
+
+
+def match_cascading_hash(x, y, min_ratio=1.75, m=None, n=2, g=2):
+    """Cascade-of-hashes match + ratio test + compaction on the GPU (the
+    'cascading-hash' branch of example/ex01_essential_estimation.py:100-105);
+    same ``m`` rule and brute-force fallback as ``nn_cascading_hash``."""
+    xrows, xdim = x.shape
+    yrows, ydim = y.shape
+    assert ydim == xdim
+    if m is None:
+        mrows = max([xrows, yrows])
+        m = int(np.floor(np.log2(mrows / 6.)))
+        if m < 4:
+            return match_bruteforcel1k2((x + 128).astype('uint8'),
+                                        (y + 128).astype('uint8'), min_ratio)
+    out = NdArray(dtype='uint64')
+    _match_cashash(x, y, xrows, yrows, xdim, m, n, g, float(min_ratio), out)
+    return _split_matches(out)
