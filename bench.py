@@ -356,8 +356,9 @@ def run_b200(args):
             roof["pipe_table_gops"] = {k: round(v["gops"], 0) for k, v in tab.items()}
     try:
         prof = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
-        roof["traffic"] = prof.get("dram_bytes_per_launch")
-        roof["traffic_source"] = prof.get("source")
+        if world == 1 and wname == "c3":      # the ncu capture is of this workload's launch
+            roof["traffic"] = prof.get("dram_bytes_per_launch")
+            roof["traffic_source"] = prof.get("source")
     except Exception:
         pass
 

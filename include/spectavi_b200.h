@@ -89,6 +89,12 @@ void spv_match_cascading_hash(const float *x, const float *y, int xrows, int yro
                               int num_hash_tables, int num_candidate_neighbours, double min_ratio,
                               NdArray *outmatches);
 
+/* The step before the matcher: spectavi/feature.py:384-407
+ * normalize_to_ubyte_and_multiple_16_dim for float32 rows -- column de-mean (float32, rows in order, as
+ * numpy sums them), scale by 128 / max|column|, round half to even, clip to [-128, 127], zero-pad the
+ * columns to a multiple of 16.  out: rows x ceil16(dim) float32, bit-identical to the numpy function. */
+void spv_normalize_to_ubyte(const float *x, int rows, int dim, NdArray *out);
+
 /* ============================ Part 2: device-resident API (device pointers)
  * Results live in a KEY buffer: uint64 keys[2][yrows], key = dist << 32 | idx,
  * all-ones = none; unsigned order of keys == the reference's (dist, idx) rule. */
@@ -113,6 +119,13 @@ int spv_keys_finalize_f32(const uint64_t *dkeys, int yrows, int kcols, uint64_t 
 size_t spv_ratio_ws_bytes(int yrows);
 int spv_ratio_matches_device(const uint64_t *dkeys, int yrows, double min_ratio, int dist_is_f32, uint8_t *dmask,
                              uint64_t *dmatches, uint32_t *dcount, void *dws, size_t ws_bytes, void *stream);
+
+/* K7: the quantiser on device rows.  dout_f32 and / or dout_u8 (= value + 128, what the matchers take;
+ * either may be NULL): rows x spv_normalize_new_dim(dim). */
+size_t spv_normalize_ws_bytes(int dim);
+int spv_normalize_new_dim(int dim);
+int spv_normalize_device(const float *dx, int rows, int dim, float *dout_f32, uint8_t *dout_u8, void *dws,
+                         size_t ws_bytes, void *stream);
 
 /* K0: (uint8)((int)v + 128), the cast of CascadingHashNn.h:236-239 (count % 4 == 0) */
 int spv_f32_to_u8_device(const float *din, uint8_t *dout, size_t count, void *stream);

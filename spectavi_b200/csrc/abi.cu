@@ -105,6 +105,16 @@ int spv_ratio_matches_device(const uint64_t* dkeys, int yrows, double min_ratio,
   return 0;
 }
 
+size_t spv_normalize_ws_bytes(int dim) { return normalize_ws_bytes(dim); }
+int spv_normalize_new_dim(int dim) { return normalize_new_dim(dim); }
+
+int spv_normalize_device(const float* dx, int rows, int dim, float* dout_f32, uint8_t* dout_u8, void* dws, size_t ws_bytes,
+                         void* stream) {
+  if (rows < 0 || dim <= 0) return fail("bad shape %d x %d", rows, dim);
+  CU_OR_FAIL(normalize_rows(dx, rows, dim, dout_f32, dout_u8, dws, ws_bytes, (cudaStream_t)stream));
+  return 0;
+}
+
 int spv_f32_to_u8_device(const float* din, uint8_t* dout, size_t count, void* stream) {
   CU_OR_FAIL(f32_to_u8(din, dout, count, (cudaStream_t)stream));
   return 0;
@@ -183,6 +193,15 @@ void spv_match_cascading_hash(const float* x, const float* y, int xrows, int yro
   const MatchSink ms = sink_for(outmatches, min_ratio);
   HostCall hc(fn);
   hc.cascade(x, y, xrows, yrows, dim, 2, hash_bit_rate, num_hash_tables, num_candidate_neighbours, nullptr, nullptr, &ms);
+}
+
+void spv_normalize_to_ubyte(const float* x, int rows, int dim, NdArray* out) {
+  const char* fn = "spv_normalize_to_ubyte";
+  if (rows < 0 || dim <= 0) die(fn, "bad shape %d x %d", rows, dim);
+  out_alloc(out, (uint64_t)rows, (uint64_t)normalize_new_dim(dim));
+  if (rows == 0) return;
+  HostCall hc(fn);
+  hc.normalize(x, rows, dim, reinterpret_cast<float*>(out->m_data));
 }
 
 static void lp_entry(const char* fn, const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k,

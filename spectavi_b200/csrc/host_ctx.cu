@@ -317,6 +317,22 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
   cudaSetDevice(prev);
 }
 
+void HostCall::normalize(const float* x, int rows, int dim, float* out) {
+  Gpu& D = g_rt.gpus[0];
+  int prev = 0;
+  cudaGetDevice(&prev);
+  CU(fn_, cudaSetDevice(D.dev));
+  const size_t ib = (size_t)rows * dim * 4, ob = (size_t)rows * normalize_new_dim(dim) * 4;
+  CU(fn_, D.xf.ensure(ib));
+  CU(fn_, D.yf.ensure(ob));
+  CU(fn_, D.rws.ensure(normalize_ws_bytes(dim)));
+  CU(fn_, cudaMemcpyAsync(D.xf.p, x, ib, cudaMemcpyHostToDevice, D.stream));
+  CU(fn_, normalize_rows((const float*)D.xf.p, rows, dim, (float*)D.yf.p, nullptr, D.rws.p, D.rws.cap, D.stream));
+  CU(fn_, cudaMemcpyAsync(out, D.yf.p, ob, cudaMemcpyDeviceToHost, D.stream));
+  CU(fn_, cudaStreamSynchronize(D.stream));
+  cudaSetDevice(prev);
+}
+
 void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p,
                    uint64_t* idx, void* dist) {
   // single GPU: the graded shapes of this entry point are small (test/test_feature.py:67-81)

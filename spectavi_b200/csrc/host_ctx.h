@@ -48,6 +48,9 @@ class HostCall {
   void cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
                uint64_t* idx, float* dist, const MatchSink* ms = nullptr);
 
+  // the quantiser (feature.py:384-407): rows x dim float32 in, rows x ceil16(dim) float32 out
+  void normalize(const float* x, int rows, int dim, float* out);
+
  private:
   void deliver_matches(const MatchSink& ms, int yrows, bool dist_f32);   // K6 on GPU 0's merged keys
   const char* fn_;

@@ -104,6 +104,30 @@ def ratio_matches(keys, min_ratio=1.75, dist_f32=False, want_mask=False):
     return (out, mask) if want_mask else out
 
 
+clib.spv_normalize_ws_bytes.restype = ct.c_size_t
+clib.spv_normalize_ws_bytes.argtypes = [ct.c_int]
+clib.spv_normalize_new_dim.restype = ct.c_int
+clib.spv_normalize_new_dim.argtypes = [ct.c_int]
+clib.spv_normalize_device.restype = ct.c_int
+clib.spv_normalize_device.argtypes = [_vp, ct.c_int, ct.c_int, _vp, _vp, _vp, ct.c_size_t, _vp]
+
+
+def normalize_rows(x, want_f32=True, want_u8=True):
+    """K7: normalize_to_ubyte_and_multiple_16_dim (feature.py:384-407) on a float32 CUDA
+    matrix.  Returns (float32 [rows, ceil16(dim)] or None, uint8 (= value + 128) or None)."""
+    assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
+    rows, dim = x.shape
+    nd = int(clib.spv_normalize_new_dim(dim))
+    nbytes = int(clib.spv_normalize_ws_bytes(dim))
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    of = torch.empty((rows, nd), dtype=torch.float32, device=x.device) if want_f32 else None
+    ou = torch.empty((rows, nd), dtype=torch.uint8, device=x.device) if want_u8 else None
+    _check(clib.spv_normalize_device(x.data_ptr(), rows, dim, of.data_ptr() if want_f32 else None,
+                                     ou.data_ptr() if want_u8 else None, ws.data_ptr(), nbytes, _stream()),
+           "spv_normalize_device")
+    return of, ou
+
+
 def nn_bruteforcel1k2_sharded(x_shard, y, xoffset, group=None):
     """Brute-force L1 k=2 with the train set sharded over the ranks of ``group``
     (SURVEY.md 8e): every rank folds its shard, the key buffers are

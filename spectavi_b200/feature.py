@@ -60,6 +60,11 @@ _match_cashash.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
                            ct.c_int, ct.c_double, ct.POINTER(NdArray)]
 
 
+_normalize = clib.spv_normalize_to_ubyte
+_normalize.restype = None
+_normalize.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"), ct.c_int, ct.c_int, ct.POINTER(NdArray)]
+
+
 def nn_bruteforce(x, y, p=.5, mu=0., k=2, use_int=False):
     """k nearest rows of ``x`` for every row of ``y`` under sum |d|^p
     (reference feature.py:246-289).  Returns ``(idx uint64, dist)`` of shape
@@ -134,6 +139,16 @@ def normalize_to_ubyte_and_multiple_16_dim(x, dtype='float32'):
     xx = np.zeros([xrows, new_dim])
     xx[:, :dim] = x0
     return xx.astype(dtype)
+
+
+def normalize_to_ubyte_and_multiple_16_dim_gpu(x):
+    """``normalize_to_ubyte_and_multiple_16_dim`` for a float32 matrix, computed on
+    the GPU (K7) and bit-identical to the numpy function above."""
+    x = np.ascontiguousarray(x, dtype='float32')
+    rows, dim = x.shape
+    out = NdArray(dtype='float32')
+    _normalize(x, rows, dim, out)
+    return out.arr.view('float32').reshape(rows, -1)
 
 
 def ratio_test(nn_dist, min_ratio=1.75):

@@ -1,0 +1,91 @@
+"""BASELINE.json configs[1] (C2): the castle image pair, vlfeat SIFT rows, brute-force L1 k=2
++ ratio test -- the reference example's step 2 (example/ex01_essential_estimation.py:89-105).
+The fixture tests/golden/castle_c2.npz holds the SIFT rows (extracted by vlfeat compiled from
+the reference tree, tests/golden/make_castle.py) and the output of the REFERENCE's own
+BruteForceNnL1K2 on them; everything here compares with ==."""
+import numpy as np
+import pytest
+
+from conftest import golden
+
+
+def _castle():
+    g = golden("castle_c2.npz")
+    s1 = np.hstack([g["k1"], g["d1"].astype("float32")])     # the 132-column rows sift_filter returns
+    s2 = np.hstack([g["k2"], g["d2"].astype("float32")])
+    return g, s1, s2
+
+
+def _step2_inputs(feature, s1, s2):
+    _x = feature.normalize_to_ubyte_and_multiple_16_dim(s1)  # ex01:92-93
+    _y = feature.normalize_to_ubyte_and_multiple_16_dim(s2)
+    return (_x + 128).astype("uint8"), (_y + 128).astype("uint8"), _x, _y
+
+
+def test_oracle_equals_reference_on_castle_128(po):
+    g, _, _ = _castle()
+    idx, dist = po.l1k2(g["d1"], g["d2"], 8)
+    assert (idx == g["idx128"].astype(np.uint64)).all() and (dist == g["dist128"]).all()
+
+
+@pytest.mark.gpu
+def test_castle_bruteforce_128(po):
+    from spectavi_b200 import feature
+    g, _, _ = _castle()
+    gi, gd = feature.nn_bruteforcel1k2(g["d1"], g["d2"])
+    assert (gi == g["idx128"].astype(np.uint64)).all() and (gd == g["dist128"]).all()
+
+
+@pytest.mark.gpu
+def test_castle_example_step2(po):
+    """normalise -> +128 -> uint8 (144-D) -> L1 k=2 -> ratio test, as the example runs it."""
+    from spectavi_b200 import feature
+    g, s1, s2 = _castle()
+    xu, yu, _, _ = _step2_inputs(feature, s1, s2)
+    assert xu.shape[1] == 144
+    gi, gd = feature.nn_bruteforcel1k2(xu, yu, nthreads=8)
+    assert (gi == g["idx"].astype(np.uint64)).all() and (gd == g["dist"]).all()
+    ratio = g["dist"][:, 1] / g["dist"][:, 0].astype("float64")      # ex01:102-105 on the reference's output
+    keep = ratio >= 1.75
+    assert (feature.ratio_test(gd, 1.75) == keep).all()
+    mx, my = feature.match_bruteforcel1k2(xu, yu, 1.75)
+    assert (my == np.nonzero(keep)[0]).all() and (mx == g["idx"][:, 0][keep]).all()
+    assert 500 < keep.sum() < 10000
+
+
+@pytest.mark.gpu
+def test_castle_device_pipeline(po):
+    """The same, device-resident end to end: K7 quantiser -> K1 -> K6, nothing but the SIFT rows
+    going in and the match list coming out."""
+    import torch
+    from spectavi_b200 import device as dev
+    g, s1, s2 = _castle()
+    _, xu = dev.normalize_rows(torch.from_numpy(s1).cuda(), want_f32=False)
+    _, yu = dev.normalize_rows(torch.from_numpy(s2).cuda(), want_f32=False)
+    keys = dev.new_keys(s2.shape[0], "cuda")
+    dev.l1k2_fold(xu, yu, keys)
+    m = dev.ratio_matches(keys, 1.75).cpu().numpy().view(np.uint64)
+    keep = g["dist"][:, 1] / g["dist"][:, 0].astype("float64") >= 1.75
+    assert (m[:, 1] == np.nonzero(keep)[0]).all() and (m[:, 0] == g["idx"][:, 0][keep]).all()
+
+
+@pytest.mark.gpu
+def test_castle_cascade_recall(po):
+    """'cascading-hash' branch of the example (ex01:100-101) with the auto parameters: distances are
+    exact L1, so a cascade neighbour is never closer than the true one, and on real SIFT rows the
+    ratio-test survivors are found (the reference's own acceptance is <= 40 % index mismatch,
+    test/test_feature.py:149-151)."""
+    from spectavi_b200 import feature
+    g, s1, s2 = _castle()
+    _, _, _x, _y = _step2_inputs(feature, s1, s2)
+    ci, cd = feature.nn_cascading_hash(_x, _y)
+    assert cd.dtype == np.float32 and ci.shape == (s2.shape[0], 2)
+    found = ci[:, 0] != np.uint64(0xFFFFFFFFFFFFFFFF)
+    assert (cd[found, 0] >= g["dist"][found, 0]).all()
+    keep = g["dist"][:, 1] / g["dist"][:, 0].astype("float64") >= 1.75
+    hit = (ci[keep, 0] == g["idx"][keep, 0].astype(np.uint64)).mean()
+    assert hit > 0.6, hit
+    mx, my = feature.match_cascading_hash(_x, _y, 1.75)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        want = cd[:, 1] / cd[:, 0].astype("float64") >= 1.75
+    assert (my == np.nonzero(want)[0]).all() and (mx == ci[:, 0][want]).all()
