@@ -134,7 +134,9 @@ size_t spv_cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g);
 /* K2-K4: cascade-of-hashes match of uint8 (value + 128) query rows dyu8 against
  * train rows dxu8 (replaces CascadingHashNn, src/CascadingHashNn.h:187-245), folded
  * into dkeys like spv_l1k2_device.  ddict: device float32 [n][dim][m] hyperplanes;
- * dict_terms: 1 if every entry is exact in bf16, else 3 (exact 3-term bf16 split). */
+ * dict_terms: 0 if every entry is q / 32 with q an int8 in [-127, 127] (the dictionary of
+ * spv_cascade_dictionary(quantize = 1): tcgen05 kind::i8 straight on the uint8 rows), 1 if every entry is
+ * exact in bf16, else 3 (exact 3-term bf16 split). */
 int spv_cascade_device(const uint8_t *dxu8, const uint8_t *dyu8, int xrows, int yrows, int dim, int m, int n, int g,
                        const float *ddict, int dict_terms, uint32_t xoffset, uint64_t *dkeys, void *dws,
                        size_t ws_bytes, void *stream);

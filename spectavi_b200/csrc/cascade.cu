@@ -291,6 +291,217 @@ __global__ void __launch_bounds__(HP_THREADS) hash_project_kernel(const HpParams
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(P.tmem_cols) : "memory");
 }
 
+// ---------------------------------------------------------------- K2, int8 path
+// The dictionary the drop-in entry point draws is q / 32 with q an int8 (cascade_dictionary,
+// quantize = true), and the rows are uint8 (value + 128), so the projection is an exact
+// integer GEMM:  32 R(row, col) = sum_k u8(row, k) * q(k, col) - 128 * sum_k q(k, col).
+// tcgen05.mma kind::i8 takes the uint8 rows AS THEY LIE IN HBM (A unsigned, B signed, int32
+// accumulators in TMEM), so nothing is converted: one TMA op per 128-row tile drops the rows
+// into shared memory already in the UMMA K-major core-matrix order (make_rows_map), one elected
+// thread issues dim/32 MMAs, and the epilogue subtracts the per-column constant.  Warp roles:
+// warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue (TMEM lane quarter = warp % 4);
+// a ring of nst row tiles and two TMEM accumulators keep load, MMA and epilogue overlapped.
+// Bound: HBM (dim bytes in, 4n (+8n) bytes out per row).  SASS: UTMALDG, UTCIMMA, LDTM.
+constexpr int HQ_THREADS = 192;
+
+struct HqParams {
+  const int8_t* img;             // [groups][dim/16][N][16] int8 hyperplane coefficients * 32
+  const int32_t* colsum;         // [groups][N]  sum_k q(k, col)
+  int rows, dim, n, m, MP, tpg, N, groups, g, nst, tmem_cols;
+  int32_t* codes;                // [n][rows]
+  unsigned long long* flips;     // [n][rows]
+};
+
+__global__ void dict_image_i8_kernel(const float* __restrict__ dict, int n, int dim, int m, int MP, int tpg, int N,
+                                     int groups, int8_t* __restrict__ img, int32_t* __restrict__ colsum) {
+  const size_t per_group = (size_t)dim * N, total = (size_t)groups * per_group;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+    const int g = (int)(e / per_group);
+    const size_t r = e % per_group;
+    const int kc = (int)(r / ((size_t)N * 16)), col = (int)((r / 16) % N), ke = (int)(r % 16);
+    const int t = g * tpg + col / MP, bit = col % MP, k = kc * 16 + ke;
+    float v = 0.f;
+    if (col / MP < tpg && t < n && bit < m) v = dict[((size_t)t * dim + k) * m + bit];
+    img[e] = (int8_t)(int)rintf(v * 32.f);
+  }
+  // column sums: one thread per (group, column); dim <= 512 terms
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < groups * N; c += gridDim.x * blockDim.x) {
+    const int g = c / N, col = c % N;
+    const int t = g * tpg + col / MP, bit = col % MP;
+    int s = 0;
+    if (col / MP < tpg && t < n && bit < m)
+      for (int k = 0; k < dim; ++k) s += (int)rintf(dict[((size_t)t * dim + k) * m + bit] * 32.f);
+    colsum[c] = s;
+  }
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_rows(uint32_t dst, const CUtensorMap* map, int row0, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst), "l"(map), "r"(0), "r"(row0), "r"(0), "r"(bar)
+      : "memory");
+}
+// kind::i8: D int32 (c_format = 2 at bits [4,6)), A uint8 (a_format = 0 at [7,10)), B int8 (b_format = 1 at
+// [10,13)), both K-major, N >> 3 at [17,23), M >> 4 at [24,29); K = 32 per instruction
+__device__ __forceinline__ uint32_t umma_idesc_u8s8(int M, int N) {
+  return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld8_i32(uint32_t taddr, int (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// one table of one row: MP accumulator columns -> code (+ least-confident bits); v = 32 R exactly
+template <int MP>
+__device__ __forceinline__ void hq_epilogue_table(uint32_t taddr, const int32_t* __restrict__ scol, int m, int nb,
+                                                  int32_t* code_out, unsigned long long* flip_out) {
+  int v[MP];
+#pragma unroll
+  for (int c = 0; c < MP; c += 8) {
+    int t8[8];
+    tmem_ld8_i32(taddr + c, t8);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[c + i] = t8[i] - 128 * scol[c + i];
+  }
+  uint32_t code = 0;   // convert_to_hashcode (CascadingHashNn.h:102-111): bit i set iff R(i) >= 0
+#pragma unroll
+  for (int b = 0; b < MP; ++b)
+    if (b < m && v[b] >= 0) code |= 1u << b;
+  *code_out = (int32_t)code;
+  if (nb > 0) {
+    // generate_y_candidate_hashcodes (:153-159): the nb smallest (|R|, bit) pairs; |v| < 2^24
+    uint32_t key[MP];
+#pragma unroll
+    for (int b = 0; b < MP; ++b) key[b] = b < m ? (((uint32_t)(v[b] < 0 ? -v[b] : v[b]) << 5) | (uint32_t)b) : 0xFFFFFFFFu;
+    unsigned long long flips = 0;
+    uint32_t last = 0;   // keys are distinct (the bit index is part of the key): take them in increasing order
+    for (int q = 0; q < nb; ++q) {
+      uint32_t best = 0xFFFFFFFFu;
+#pragma unroll
+      for (int b = 0; b < MP; ++b) {
+        const uint32_t k = (q == 0 || key[b] > last) ? key[b] : 0xFFFFFFFFu;
+        best = k < best ? k : best;
+      }
+      last = best;
+      flips |= (unsigned long long)(best & 31u) << (5 * q);
+    }
+    *flip_out = flips;
+  }
+}
+
+__global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __grid_constant__ CUtensorMap tmA, const HqParams P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int dim = P.dim, N = P.N, nst = P.nst;
+  const uint32_t stage_bytes = (uint32_t)HP_ROWS * dim;      // [dim/16][128 rows][16 B]
+  unsigned char* sA = smem;
+  unsigned char* sB = sA + (size_t)nst * stage_bytes;         // [dim/16][N][16 B]
+  int32_t* sCol = reinterpret_cast<int32_t*>(sB + (size_t)dim * N);
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(sCol + N + (N & 1));
+  const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nst, bar_tfull = bar_empty + 8 * nst,
+                 bar_tempty = bar_tfull + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * nst + 4);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int s = 0; s < nst; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 128); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(P.tmem_cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t idesc = umma_idesc_u8s8(HP_ROWS, N);
+  const int ntiles = (P.rows + HP_ROWS - 1) / HP_ROWS;
+  const int my_tiles = blockIdx.x < ntiles ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+  for (int grp = 0; grp < P.groups; ++grp) {
+    {   // B operand and column constants of this group of tables
+      const uint4* src = reinterpret_cast<const uint4*>(P.img + (size_t)grp * dim * N);
+      uint4* dst = reinterpret_cast<uint4*>(sB);
+      for (int e = tid; e < dim * N / 16; e += HQ_THREADS) dst[e] = src[e];
+      for (int e = tid; e < N; e += HQ_THREADS) sCol[e] = P.colsum[grp * N + e];
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    const uint32_t it0 = (uint32_t)grp * (uint32_t)my_tiles;   // the same iteration count in every role
+    if (warp == 0) {
+      if (lane == 0)
+        for (int j = 0; j < my_tiles; ++j) {
+          const uint32_t it = it0 + j, s = it % nst, ph = (it / nst) & 1u;
+          mbar_wait(bar_empty + 8 * s, ph ^ 1u);
+          mbar_expect_tx(bar_full + 8 * s, stage_bytes);
+          tma_load_rows(smem_u32(sA) + s * stage_bytes, &tmA, (blockIdx.x + j * gridDim.x) * HP_ROWS, bar_full + 8 * s);
+        }
+    } else if (warp == 1) {
+      if (lane == 0)
+        for (int j = 0; j < my_tiles; ++j) {
+          const uint32_t it = it0 + j, s = it % nst, ph = (it / nst) & 1u, a = it & 1u, aph = (it >> 1) & 1u;
+          mbar_wait(bar_tempty + 8 * a, aph ^ 1u);     // the epilogue has drained this accumulator
+          mbar_wait(bar_full + 8 * s, ph);             // the row tile has landed
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a0 = smem_u32(sA) + s * stage_bytes, b0 = smem_u32(sB);
+          for (int k = 0; k < dim / 32; ++k) {         // one UMMA per K = 32 bytes = two 16-byte k-chunks
+            const uint64_t ad = umma_desc(a0 + (2 * k) * (HP_ROWS * 16), HP_ROWS * 16, 128);
+            const uint64_t bd = umma_desc(b0 + (2 * k) * (N * 16), N * 16, 128);
+            umma_i8(tmem + a * N, ad, bd, idesc, k != 0);
+          }
+          umma_commit(bar_empty + 8 * s);              // the stage may be refilled once these MMAs have read it
+          umma_commit(bar_tfull + 8 * a);              // ... and the accumulator may be read
+        }
+    } else {
+      const int quarter = warp & 3;                    // TMEM lanes 32 * (warp % 4) ..
+      for (int j = 0; j < my_tiles; ++j) {
+        const uint32_t it = it0 + j, a = it & 1u, aph = (it >> 1) & 1u;
+        mbar_wait(bar_tfull + 8 * a, aph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int row = (blockIdx.x + j * gridDim.x) * HP_ROWS + quarter * 32 + lane;
+        for (int tg = 0; tg < P.tpg; ++tg) {
+          const int t = grp * P.tpg + tg;
+          if (t >= P.n) break;
+          const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * N + tg * P.MP;
+          int32_t code;
+          unsigned long long fl = 0;
+          if (P.MP == 8) hq_epilogue_table<8>(taddr, sCol + tg * 8, P.m, P.g, &code, &fl);
+          else if (P.MP == 16) hq_epilogue_table<16>(taddr, sCol + tg * 16, P.m, P.g, &code, &fl);
+          else if (P.MP == 24) hq_epilogue_table<24>(taddr, sCol + tg * 24, P.m, P.g, &code, &fl);
+          else hq_epilogue_table<32>(taddr, sCol + tg * 32, P.m, P.g, &code, &fl);
+          if (row < P.rows) {
+            P.codes[(size_t)t * P.rows + row] = code;
+            if (P.g > 0) P.flips[(size_t)t * P.rows + row] = fl;
+          }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(bar_tempty + 8 * a);
+      }
+    }
+    __syncthreads();   // every tile of the group is through its epilogue, hence through its MMAs: sB is free
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(P.tmem_cols) : "memory");
+}
+
 // ---------------------------------------------------------------- K3: CSR buckets
 // Bucket key = code & (2^mb - 1), mb = min(m, 24) (full codes are re-checked in K4
 // when m > 24).  All tables share one count/offset array of n * 2^mb entries and
@@ -631,9 +842,57 @@ bool make_plan(int xrows, int yrows, int dim, int m, int n, int g, int terms, Pl
   return true;
 }
 
+// shared memory and ring depth of the int8 kernel; nst = 0: does not fit, use the bf16 kernel
+size_t i8_smem(const Plan& pl, int dim, int* nst_out) {
+  const size_t stage = (size_t)HP_ROWS * dim, fixed = (size_t)dim * pl.N + 4 * (size_t)(pl.N + 1) + 8 * 24 + 64 + 1024;
+  int nst = 0;
+  if (fixed + 2 * stage <= 200 * 1024) {
+    nst = (int)((100 * 1024 > fixed ? 100 * 1024 - fixed : 0) / stage);
+    nst = nst < 2 ? 2 : (nst > 8 ? 8 : nst);
+  }
+  *nst_out = nst;
+  return fixed + (size_t)nst * stage;
+}
+
+// dict_terms 0 (int8-exact dictionary): the int8 kernel when its tiles fit, else the bf16 kernel (1 term is exact too)
+bool plan_for(int xrows, int yrows, int dim, int m, int n, int g, int dict_terms, Plan* pl) {
+  if (!make_plan(xrows, yrows, dim, m, n, g, dict_terms == 0 ? 1 : dict_terms, pl)) return false;
+  if (dict_terms == 0) {
+    int nst = 0;
+    i8_smem(*pl, dim, &nst);
+    if (nst > 0 && dim % 32 == 0) pl->terms = 0;
+  }
+  return true;
+}
+
+cudaError_t run_project_i8(const Plan& pl, const uint8_t* rows_u8, int rows, int dim, int n, int m, int g, const void* img,
+                           int32_t* codes, unsigned long long* flips, int sms, cudaStream_t stream) {
+  int nst = 0;
+  const size_t smem = i8_smem(pl, dim, &nst);
+  HqParams hq;
+  hq.img = static_cast<const int8_t*>(img);
+  hq.colsum = reinterpret_cast<const int32_t*>(static_cast<const unsigned char*>(img) + align256((size_t)pl.groups * dim * pl.N));
+  hq.rows = rows; hq.dim = dim; hq.n = n; hq.m = m; hq.MP = pl.MP; hq.tpg = pl.tpg; hq.N = pl.N; hq.groups = pl.groups;
+  hq.g = g; hq.nst = nst; hq.codes = codes; hq.flips = flips;
+  int cols = 32;
+  while (cols < 2 * pl.N) cols <<= 1;
+  hq.tmem_cols = cols;
+  CUtensorMap tmA;
+  if (!make_rows_map(&tmA, rows_u8, rows, dim, HP_ROWS)) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(hash_project_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int per_sm = (smem <= 110 * 1024 && cols <= 256) ? 2 : 1;
+  const int ntiles = (rows + HP_ROWS - 1) / HP_ROWS;
+  const int grid = ntiles < sms * per_sm ? ntiles : sms * per_sm;
+  hash_project_i8_kernel<<<grid, HQ_THREADS, smem, stream>>>(tmA, hq);
+  count_launch();
+  return cudaGetLastError();
+}
+
 cudaError_t run_project(const Plan& pl, const uint8_t* rows_u8, int rows, int dim, int n, int m, int g,
                         const __nv_bfloat16* img, int32_t* codes, unsigned long long* flips, int sms, cudaStream_t stream) {
   if (rows <= 0) return cudaSuccess;
+  if (pl.terms == 0) return run_project_i8(pl, rows_u8, rows, dim, n, m, g, img, codes, flips, sms, stream);
   HpParams hp;
   hp.rows_u8 = rows_u8; hp.img = img; hp.rows = rows; hp.dim = dim; hp.n = n; hp.m = m; hp.MP = pl.MP; hp.tpg = pl.tpg;
   hp.N = pl.N; hp.groups = pl.groups; hp.terms = pl.terms; hp.g = g; hp.codes = codes; hp.flips = flips;
@@ -649,6 +908,17 @@ cudaError_t run_project(const Plan& pl, const uint8_t* rows_u8, int rows, int di
   hash_project_kernel<<<grid, HP_THREADS, pl.smem_hp, stream>>>(hp);
   count_launch();
   return cudaGetLastError();
+}
+
+void build_image(const Plan& pl, const float* ddict, int n, int dim, int m, __nv_bfloat16* img, cudaStream_t stream) {
+  if (pl.terms == 0) {
+    int8_t* q = reinterpret_cast<int8_t*>(img);
+    int32_t* cs = reinterpret_cast<int32_t*>(reinterpret_cast<unsigned char*>(img) + align256((size_t)pl.groups * dim * pl.N));
+    dict_image_i8_kernel<<<64, 256, 0, stream>>>(ddict, n, dim, m, pl.MP, pl.tpg, pl.N, pl.groups, q, cs);
+  } else {
+    dict_image_kernel<<<64, 256, 0, stream>>>(ddict, n, dim, m, pl.MP, pl.tpg, pl.N, img);
+  }
+  count_launch();
 }
 
 }  // namespace
@@ -674,15 +944,14 @@ cudaError_t hash_codes(const uint8_t* drows, int rows, int dim, int m, int n, in
                        int32_t* codes, unsigned long long* flips, void* ws, size_t ws_bytes, cudaStream_t stream) {
   if (rows <= 0) return cudaSuccess;
   Plan pl;
-  if (dict_terms != 1 && dict_terms != 3) return cudaErrorInvalidValue;
-  if (!make_plan(rows, rows, dim, m, n, g, dict_terms, &pl) || ws_bytes < pl.total) return cudaErrorInvalidValue;
+  if (dict_terms != 0 && dict_terms != 1 && dict_terms != 3) return cudaErrorInvalidValue;
+  if (!plan_for(rows, rows, dim, m, n, g, dict_terms, &pl) || ws_bytes < pl.total) return cudaErrorInvalidValue;
   int dev = 0, sms = 0;
   cudaError_t e;
   if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
   if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
   __nv_bfloat16* img = reinterpret_cast<__nv_bfloat16*>(static_cast<unsigned char*>(ws) + pl.o_img);
-  dict_image_kernel<<<64, 256, 0, stream>>>(ddict, n, dim, m, pl.MP, pl.tpg, pl.N, img);
-  count_launch();
+  build_image(pl, ddict, n, dim, m, img, stream);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   return run_project(pl, drows, rows, dim, n, m, g > 0 ? pl.nb : 0, img, codes, flips, sms, stream);
 }
@@ -692,8 +961,8 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
                           size_t ws_bytes, cudaStream_t stream) {
   if (yrows <= 0 || xrows <= 0) return cudaSuccess;   // nothing to fold in
   Plan pl;
-  if (dict_terms != 1 && dict_terms != 3) return cudaErrorInvalidValue;
-  if (!make_plan(xrows, yrows, dim, m, n, g, dict_terms, &pl) || ws_bytes < pl.total) return cudaErrorInvalidValue;
+  if (dict_terms != 0 && dict_terms != 1 && dict_terms != 3) return cudaErrorInvalidValue;
+  if (!plan_for(xrows, yrows, dim, m, n, g, dict_terms, &pl) || ws_bytes < pl.total) return cudaErrorInvalidValue;
   int dev = 0, sms = 0;
   cudaError_t e;
   if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
@@ -707,8 +976,7 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
   int32_t* ids = reinterpret_cast<int32_t*>(w + pl.o_ids);
   uint32_t* sums = reinterpret_cast<uint32_t*>(w + pl.o_sums);
 
-  dict_image_kernel<<<64, 256, 0, stream>>>(ddict, n, dim, m, pl.MP, pl.tpg, pl.N, img);
-  count_launch();
+  build_image(pl, ddict, n, dim, m, img, stream);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   // train side: codes, then CSR buckets (initialize_hash_tables, :187-196)
   if ((e = run_project(pl, dxu8, xrows, dim, n, m, 0, img, xcodes, nullptr, sms, stream)) != cudaSuccess) return e;

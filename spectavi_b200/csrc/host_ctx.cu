@@ -279,7 +279,7 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
     const int x0 = gi * per < xrows ? gi * per : xrows;
     const int xn = (x0 + per <= xrows) ? per : xrows - x0;
     CU(fn_, cudaSetDevice(D.dev));
-    CU(fn_, cascade_match((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, m, n, g, (const float*)D.dict.p, 1,
+    CU(fn_, cascade_match((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, m, n, g, (const float*)D.dict.p, 0,
                           (uint32_t)x0, (unsigned long long*)D.keys.p, D.ws.p, D.ws.cap, D.stream));
   }
   Gpu& R = g_rt.gpus[0];

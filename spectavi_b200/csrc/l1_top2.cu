@@ -371,7 +371,9 @@ EncodeTiledFn encode_tiled() {
 // (1, dim, 16); box = (16, box_rows, dim/16) = one whole tile, delivered to shared
 // memory k-chunk-major.  Measured (tools/ubench_tma_box.cu): one such op fills an
 // 8 KB stage in 544 cycles with 148 SMs streaming, vs 850 as 8 separate 16 B boxes.
-bool make_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows) {
+}  // namespace
+
+bool make_rows_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows) {
   EncodeTiledFn enc = encode_tiled();
   if (!enc) return false;
   cuuint64_t gdim[3] = {16u, (cuuint64_t)rows, (cuuint64_t)(dim / 16)};
@@ -382,6 +384,8 @@ bool make_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_
              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
+
+namespace {
 
 cudaError_t launch_tiled(const CUtensorMap& tmx, const CUtensorMap& tmy, Params p, int sms, cudaStream_t stream) {
   // as many ring stages as fit beside the query tile: the ring is also the slack
@@ -444,7 +448,7 @@ cudaError_t l1_top2_u8(const uint8_t* dx, const uint8_t* dy, int xrows, int yrow
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e != cudaSuccess) return e;
   CUtensorMap tmx, tmy;
-  if (!make_map(&tmx, dx, xrows, dim, BX) || !make_map(&tmy, dy, yrows, dim, BY)) return cudaErrorInvalidValue;
+  if (!make_rows_map(&tmx, dx, xrows, dim, BX) || !make_rows_map(&tmy, dy, yrows, dim, BY)) return cudaErrorInvalidValue;
   Params p;
   p.xrows = xrows; p.yrows = yrows; p.nk16 = dim / 16; p.xoffset = xoffset;
   p.nxt = (xrows + BX - 1) / BX; p.nyt = (yrows + BY - 1) / BY;

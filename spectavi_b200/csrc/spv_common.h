@@ -9,6 +9,7 @@
 // "no neighbour" (BruteForceNnL1K2.h:99-103: dist INT_MAX, idx (size_t)-1) is
 // the all-ones key, which loses every comparison.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -38,6 +39,10 @@ cudaError_t keys_finalize_i32(const unsigned long long* keys, int yrows, int kco
 // same but distances as float (CascadingHashNn.h:244 casts int -> float)
 cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx,
                               float* dist, cudaStream_t stream);
+// TMA view of a row-major rows x dim uint8 matrix as (16 B, rows, dim/16) with byte strides (1, dim, 16):
+// a box of (16, box_rows, dim/16) lands in shared memory as [dim/16][box_rows][16 B], i.e. already in the
+// k-chunk-major order K1 reads and in the UMMA K-major no-swizzle core-matrix order K2 feeds to tcgen05
+bool make_rows_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows);
 // ---- lp_topk.cu : K1f, brute-force sum |x-y|^p top-k over float32 / int32 rows
 // (BruteForceNn.h:37-120).  partial: scratch of lp_partial_bytes(); didx/ddist:
 // yrows x k outputs in the reference's layout (ascending, right-aligned).

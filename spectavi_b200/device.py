@@ -190,9 +190,15 @@ def _ws(xrows, yrows, dim, m, n, g, device):
 
 
 def dict_terms_of(dictionary):
-    """1 when every hyperplane coefficient is exact in bf16, else 3."""
+    """How K2 may multiply by this dictionary exactly: 0 when every coefficient is q / 32 with q an
+    int8 in [-127, 127] (the library's own quantised dictionary: tcgen05 kind::i8 on the raw uint8
+    rows), 1 when every coefficient is exact in bf16, else 3 (exact 3-term bf16 split)."""
     d = dictionary if torch.is_tensor(dictionary) else torch.from_numpy(_np.ascontiguousarray(dictionary))
-    return 1 if bool((d.float().bfloat16().float() == d.float()).all()) else 3
+    d = d.float()
+    q = d * 32.0
+    if bool(((q == q.round()) & (q.abs() <= 127)).all()):
+        return 0
+    return 1 if bool((d.bfloat16().float() == d).all()) else 3
 
 
 def hash_codes(rows_u8, dictionary, g=0, dict_terms=None):

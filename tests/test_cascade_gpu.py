@@ -60,14 +60,16 @@ def _probe_sets(codes, flips, nb):
 
 @pytest.mark.parametrize("shape", [(1000, 128, 17, 2, 2), (300, 144, 8, 16, 5), (257, 16, 5, 3, 7), (129, 512, 31, 2, 3),
                                    (500, 256, 24, 5, 0), (64, 128, 9, 9, 4)])
-def test_hash_codes_bit_exact_quantised_dictionary(po, dev, shape):
+@pytest.mark.parametrize("terms", [0, 1, 3])    # 0: tcgen05 kind::i8 on the raw uint8 rows; 1 / 3: bf16 terms
+def test_hash_codes_bit_exact_quantised_dictionary(po, dev, shape, terms):
     import torch
     rows, dim, m, n, g = shape
     rng = np.random.RandomState(rows + m)
     x = _quantised_rows(rng, rows, dim)
     d = dev.cascade_dictionary(dim, m, n, seed=rows)
-    assert dev.dict_terms_of(d) == 1
-    codes, flips = dev.hash_codes(torch.from_numpy((x + 128).astype("uint8")).cuda(), torch.from_numpy(d), g)
+    assert dev.dict_terms_of(d) == 0
+    codes, flips = dev.hash_codes(torch.from_numpy((x + 128).astype("uint8")).cuda(), torch.from_numpy(d), g,
+                                  dict_terms=terms)
     codes = codes.cpu().numpy()
     want = po.hashcodes(x, d)                      # [rows][n]
     assert (codes.T == want).all()
@@ -177,3 +179,21 @@ def test_reference_acceptance_test(po, feature):
     gi, _ = feature.nn_cascading_hash(x, y, m=8, n=16, g=5)
     ti, _ = po.numpy_l1k2((x + 128).astype("uint8"), (y + 128).astype("uint8"))
     assert (gi != ti).sum() <= 2 * round(.4 * 200)
+
+
+@pytest.mark.parametrize("rows,dim,m,n,g", [(100_003, 128, 14, 2, 2), (40_001, 64, 10, 12, 3), (33_000, 256, 20, 3, 2),
+                                            (5_000, 512, 12, 2, 2), (20_000, 32, 11, 30, 1)])
+def test_hash_codes_i8_pipeline_many_tiles(po, dev, rows, dim, m, n, g):
+    """The persistent TMA -> tcgen05 kind::i8 -> TMEM -> epilogue pipeline over hundreds of row tiles per
+    CTA, ragged last tile, several table groups: codes == the bf16 kernel's == the oracle's (sampled)."""
+    import torch
+    rng = np.random.RandomState(rows + dim)
+    x = _quantised_rows(rng, rows, dim)
+    d = dev.cascade_dictionary(dim, m, n, seed=dim)
+    xu = torch.from_numpy((x + 128).astype("uint8")).cuda()
+    c0, f0 = dev.hash_codes(xu, torch.from_numpy(d), g, dict_terms=0)
+    c1, f1 = dev.hash_codes(xu, torch.from_numpy(d), g, dict_terms=1)
+    assert bool((c0 == c1).all()) and bool((f0 == f1).all())
+    sel = rng.choice(rows, 3000, replace=False)
+    want = po.hashcodes(x[sel], d)
+    assert (c0.cpu().numpy().T[sel] == want).all()

@@ -25,6 +25,7 @@ src = torch.randint(0, rows, (half,), device="cuda", generator=gen)
 noise = torch.randint(-3, 4, (half, dim), device="cuda", generator=gen)
 y[:half] = (x[src].to(torch.int32) + noise).clamp(0, 255).to(torch.uint8)
 dic = torch.from_numpy(dev.cascade_dictionary(dim, m, n)).cuda()
+terms = dev.dict_terms_of(dic)   # 0: int8-exact dictionary -> tcgen05 kind::i8 projection
 
 def timed(fn, reps):
     fn(); torch.cuda.synchronize()
@@ -38,12 +39,12 @@ def timed(fn, reps):
 keys = dev.new_keys(rows, "cuda")
 def cascade():
     dev.keys_reset(keys)
-    ws = dev.cascade_fold(x, y, keys, dic, g, 0, dict_terms=1)
+    ws = dev.cascade_fold(x, y, keys, dic, g, 0, dict_terms=terms)
     return dev.keys_finalize(keys, 2, torch.float32), ws
 l0 = dev.launch_count()
 ms_c, ((ci, cd), _) = timed(cascade, reps)
 launches = (dev.launch_count() - l0) // (reps + 1)
-ms_codes, _ = timed(lambda: dev.hash_codes(x, dic, 0, dict_terms=1), reps)
+ms_codes, _ = timed(lambda: dev.hash_codes(x, dic, 0, dict_terms=terms), reps)
 
 bkeys = dev.new_keys(rows, "cuda")
 def brute():
