@@ -299,10 +299,12 @@ __global__ void __launch_bounds__(HP_THREADS) hash_project_kernel(const HpParams
 // accumulators in TMEM), so nothing is converted: one TMA op per 128-row tile drops the rows
 // into shared memory already in the UMMA K-major core-matrix order (make_rows_map), one elected
 // thread issues dim/32 MMAs, and the epilogue subtracts the per-column constant.  Warp roles:
-// warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue (TMEM lane quarter = warp % 4);
+// warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue (TMEM lane quarter = warp % 4, two warps per
+// quarter taking alternate tables);
 // a ring of nst row tiles and two TMEM accumulators keep load, MMA and epilogue overlapped.
 // Bound: HBM (dim bytes in, 4n (+8n) bytes out per row).  SASS: UTMALDG, UTCIMMA, LDTM.
-constexpr int HQ_THREADS = 192;
+constexpr int HQ_EPI_WARPS = 8;                       // two per TMEM lane quarter, tables split between them
+constexpr int HQ_THREADS = (2 + HQ_EPI_WARPS) * 32;
 
 struct HqParams {
   const int8_t* img;             // [groups][dim/16][N][16] int8 hyperplane coefficients * 32
@@ -381,8 +383,8 @@ __device__ __forceinline__ void hq_epilogue_table(uint32_t taddr, const int32_t*
   }
   uint32_t code = 0;   // convert_to_hashcode (CascadingHashNn.h:102-111): bit i set iff R(i) >= 0
 #pragma unroll
-  for (int b = 0; b < MP; ++b)
-    if (b < m && v[b] >= 0) code |= 1u << b;
+  for (int b = MP - 1; b >= 0; --b) code = code * 2u + (~(uint32_t)v[b] >> 31);
+  code &= (m >= 32) ? 0xFFFFFFFFu : ((1u << m) - 1u);
   *code_out = (int32_t)code;
   if (nb > 0) {
     // generate_y_candidate_hashcodes (:153-159): the nb smallest (|R|, bit) pairs; |v| < 2^24
@@ -420,7 +422,7 @@ __global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __gri
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int s = 0; s < nst; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 128); }
+    for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, HQ_EPI_WARPS * 32); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -471,12 +473,13 @@ __global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __gri
         }
     } else {
       const int quarter = warp & 3;                    // TMEM lanes 32 * (warp % 4) ..
+      const int half = (warp - 2) >> 2;                // which of the two warps of this quarter
       for (int j = 0; j < my_tiles; ++j) {
         const uint32_t it = it0 + j, a = it & 1u, aph = (it >> 1) & 1u;
         mbar_wait(bar_tfull + 8 * a, aph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int row = (blockIdx.x + j * gridDim.x) * HP_ROWS + quarter * 32 + lane;
-        for (int tg = 0; tg < P.tpg; ++tg) {
+        for (int tg = half; tg < P.tpg; tg += HQ_EPI_WARPS / 4) {
           const int t = grp * P.tpg + tg;
           if (t >= P.n) break;
           const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + a * N + tg * P.MP;
