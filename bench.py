@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-peak", action="store_true", help="skip the pipe-peak microbenchmark")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C2 (castle) and C5 (cascade) side measurements")
     return ap.parse_args()
 
 
@@ -150,9 +151,9 @@ def cpu_sample(x, yfull, budget_s, cores):
     rows = max(cores, rows // cores * cores)
     ys = np.ascontiguousarray(yfull[:rows])
     t0 = time.perf_counter()
-    fn(x, ys, cores)
+    res = fn(x, ys, cores)
     dt = time.perf_counter() - t0
-    return kind, x.shape[0] * rows / dt / 1e9, rows, dt
+    return kind, x.shape[0] * rows / dt / 1e9, rows, dt, res
 
 
 def run_reference(args):
@@ -210,6 +211,47 @@ def pipe_peak(dev_index):
         return None
     tab = {names[v].decode(): {"ops_per_clk_sm": out[2 * v], "gops": out[2 * v + 1]} for v in range(n)}
     return tab
+
+
+def side_measurements(device):
+    """Not part of the metric: BASELINE.json's other configs measured in the same run, for the record.
+    c2: the castle pair's SIFT rows (tests/golden/castle_c2.npz) through the example's step 2 via the
+    host-buffer API; c5: the cascade-of-hashes matcher at 1M x 1M against brute force (tools/bench_cascade.py)."""
+    import numpy as np
+    out = {}
+    try:
+        from spectavi_b200 import feature
+        g = np.load(os.path.join(ROOT, "tests", "golden", "castle_c2.npz"))
+        s1 = np.hstack([g["k1"], g["d1"].astype("float32")])
+        s2 = np.hstack([g["k2"], g["d2"].astype("float32")])
+        xu = (feature.normalize_to_ubyte_and_multiple_16_dim(s1) + 128).astype("uint8")
+        yu = (feature.normalize_to_ubyte_and_multiple_16_dim(s2) + 128).astype("uint8")
+        feature.nn_bruteforcel1k2(xu, yu)
+        best = 1e9
+        for _ in range(5):
+            t0 = time.perf_counter(); gi, gd = feature.nn_bruteforcel1k2(xu, yu); best = min(best, time.perf_counter() - t0)
+        t0 = time.perf_counter(); mx, my = feature.match_bruteforcel1k2(xu, yu, 1.75); tm = time.perf_counter() - t0
+        cpu_ms = None
+        try:
+            from oracle import pyoracle as po
+            cfn = po.ref_l1k2 if po.have_ref() else po.l1k2
+            t0 = time.perf_counter(); cfn(xu, yu, os.cpu_count() or 1); cpu_ms = (time.perf_counter() - t0) * 1e3
+        except Exception:
+            pass
+        out["c2_castle"] = {"rows": [int(xu.shape[0]), int(yu.shape[0])], "dim": int(xu.shape[1]),
+                            "cpu_reference_ms(all host cores, real SIFT rows: the prune of BruteForceNnL1K2.h:118-121 bites)": cpu_ms,
+                            "nn_bruteforcel1k2_ms_e2e": best * 1e3, "Gpairs_per_s_e2e": xu.shape[0] * yu.shape[0] / best / 1e9,
+                            "match_ms_e2e": tm * 1e3, "matches": int(mx.shape[0]),
+                            "equals_reference_output": bool((gi == g["idx"].astype(np.uint64)).all() and (gd == g["dist"]).all())}
+    except Exception as ex:                                  # a side measurement must never cost the bench line
+        out["c2_castle"] = {"error": repr(ex)[:200]}
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_cascade
+        out["c5_cascade"] = bench_cascade.run(1_000_000, 128, 3, 1000)
+    except Exception as ex:
+        out["c5_cascade"] = {"error": repr(ex)[:200]}
+    return out
 
 
 def run_b200(args):
@@ -366,17 +408,20 @@ def run_b200(args):
     if not args.no_cpu:
         cores = os.cpu_count() or 1
         xfull = hx.numpy() if world == 1 else host_rows(xr, dim, 11)
-        kind, gps, rows, secs = cpu_sample(xfull, hy.numpy(), args.cpu_seconds, cores)
+        kind, gps, rows, secs, (oi, od) = cpu_sample(xfull, hy.numpy(), args.cpu_seconds, cores)
         cpu = {"value": gps, "unit": UNIT, "cores": cores, "kind": kind,
                "sample": "first %d of %d query rows x all %d train rows, %.1f s wall, extrapolated by rows (rows independent)" % (rows, yr, xr, secs)}
         if world == 1:
-            # the CPU leg's results double as a parity check of the timed GPU output
-            from oracle import pyoracle as po
-            oi, od = (po.ref_l1k2 if kind == "reference" else po.l1k2)(xfull, np.ascontiguousarray(hy.numpy()[:min(rows, 256)]), cores)
+            # the CPU leg's results double as a parity check of the timed GPU output: every sampled query row
+            oi, od = oi.reshape(-1, 2), od.reshape(-1, 2)
             gi = result_idx[:oi.shape[0]].cpu().numpy().view(np.uint64)
             gd = result_dist[:oi.shape[0]].cpu().numpy()
             cpu["parity_rows_checked"] = int(oi.shape[0])
             cpu["parity_bit_exact"] = bool((gi == oi).all() and (gd == od).all())
+
+    extras = None
+    if world == 1 and not args.no_extras:
+        extras = side_measurements(device)
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3) if args.warmup else 0, "ms_per_step": step_ms / args.steps,
@@ -387,6 +432,8 @@ def run_b200(args):
                        "l2": "L2 flushed between timed steps by a %d MiB fill outside the event pair" % (L2_FLUSH_BYTES >> 20),
                        "timing": "CUDA events per step on the launching stream, summed, max over ranks"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(l1 - l0), "roofline": roof, "cpu_baseline": cpu}
+    if extras:
+        line["extras"] = extras
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -147,14 +147,22 @@ __device__ __noinline__ void offer(unsigned long long* best, uint32_t dist, uint
   if (loser != KEY_NONE) atomicMin(best + BY, loser);
 }
 
+// Half a k-chunk (8 dims) of the 8 x 8 register tile.  Operands are loaded by kload() one half-chunk AHEAD
+// of the ksad() that consumes them (two register sets of 16 x 8 B, the same 64 registers a whole chunk of
+// 16 LDS.128 would take), so the 16 LDS.64 of the next half are in flight under the 128 VABSDIFF4 of this
+// one instead of in front of them.  (9 warps per CTA cap the kernel at 168 registers -- three warps share
+// one scheduler's 16 K registers -- so a second set of full 16-byte operands does not fit.)
+__device__ __forceinline__ void kload(uint2 (&ra)[TY], uint2 (&rb)[TX], const uint2* __restrict__ ys,
+                                      const uint2* __restrict__ xs) {
+#pragma unroll
+  for (int i = 0; i < TY; ++i) ra[i] = ys[i * 8];    // rows ly + 4 i   (uint2 units: 2 per 16-byte row slot)
+#pragma unroll
+  for (int j = 0; j < TX; ++j) rb[j] = xs[j * 16];   // rows lx + 8 j
+}
+
 template <bool FIRST>
-__device__ __forceinline__ void kstep(uint32_t (&acc)[TY][TX], const uint32_t (&negthr)[TY], const uint4* __restrict__ ys,
-                                      const uint4* __restrict__ xs) {
-  uint4 ra[TY], rb[TX];
-#pragma unroll
-  for (int i = 0; i < TY; ++i) ra[i] = ys[i * 4];   // rows ly + 4 i
-#pragma unroll
-  for (int j = 0; j < TX; ++j) rb[j] = xs[j * 8];   // rows lx + 8 j
+__device__ __forceinline__ void ksad(uint32_t (&acc)[TY][TX], const uint32_t (&negthr)[TY], const uint2 (&ra)[TY],
+                                     const uint2 (&rb)[TX]) {
 #pragma unroll
   for (int i = 0; i < TY; ++i)
 #pragma unroll
@@ -163,14 +171,6 @@ __device__ __forceinline__ void kstep(uint32_t (&acc)[TY][TX], const uint32_t (&
   for (int i = 0; i < TY; ++i)
 #pragma unroll
     for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].y, rb[j].y, acc[i][j]);
-#pragma unroll
-  for (int i = 0; i < TY; ++i)
-#pragma unroll
-    for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].z, rb[j].z, acc[i][j]);
-#pragma unroll
-  for (int i = 0; i < TY; ++i)
-#pragma unroll
-    for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].w, rb[j].w, acc[i][j]);
 }
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -268,9 +268,23 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     }
     mbar_wait(bar_full + 8 * stage, phase);
     const uint4* xs = xs0 + stage * xstage_u4;
-    kstep<true>(acc, negthr, ys, xs);
+    {
+      // half-chunk h = 2 c + (0 | 1): the 8-byte halves of chunk c sit at byte offsets 0 and 8 of the 16-byte slots
+      const uint2* y2 = reinterpret_cast<const uint2*>(ys);
+      const uint2* x2 = reinterpret_cast<const uint2*>(xs);
+      uint2 raA[TY], rbA[TX], raB[TY], rbB[TX];
+      kload(raA, rbA, y2, x2);
+      kload(raB, rbB, y2 + 1, x2 + 1);
+      ksad<true>(acc, negthr, raA, rbA);
 #pragma unroll 1
-    for (int c = 1; c < nk16; ++c) kstep<false>(acc, negthr, ys + c * BY, xs + c * BX);
+      for (int c = 1; c < nk16; ++c) {     // entering: B holds the second half of chunk c - 1
+        kload(raA, rbA, y2 + c * (2 * BY), x2 + c * (2 * BX));
+        ksad<false>(acc, negthr, raB, rbB);
+        kload(raB, rbB, y2 + c * (2 * BY) + 1, x2 + c * (2 * BX) + 1);
+        ksad<false>(acc, negthr, raA, rbA);
+      }
+      ksad<false>(acc, negthr, raB, rbB);
+    }
     __syncwarp();
     if (lane == 0) mbar_arrive(bar_empty + 8 * stage);   // operands are in registers: release the stage
 

@@ -11,61 +11,67 @@ import torch
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 from spectavi_b200 import device as dev
 
-rows = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
-dim = int(sys.argv[2]) if len(sys.argv) > 2 else 128
-reps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
-cpu_rows = int(sys.argv[4]) if len(sys.argv) > 4 else 2000
-m = int(np.floor(np.log2(rows / 6.)))          # feature.py:364-367
-n, g = 2, 2
-gen = torch.Generator(device="cuda").manual_seed(3)
-x = torch.randint(0, 256, (rows, dim), dtype=torch.uint8, device="cuda", generator=gen)
-y = torch.randint(0, 256, (rows, dim), dtype=torch.uint8, device="cuda", generator=gen)
-half = rows // 2
-src = torch.randint(0, rows, (half,), device="cuda", generator=gen)
-noise = torch.randint(-3, 4, (half, dim), device="cuda", generator=gen)
-y[:half] = (x[src].to(torch.int32) + noise).clamp(0, 255).to(torch.uint8)
-dic = torch.from_numpy(dev.cascade_dictionary(dim, m, n)).cuda()
-terms = dev.dict_terms_of(dic)   # 0: int8-exact dictionary -> tcgen05 kind::i8 projection
 
-def timed(fn, reps):
-    fn(); torch.cuda.synchronize()
-    best = 1e30
-    for _ in range(reps):
-        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-        e0.record(); out = fn(); e1.record(); torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1))
-    return best, out
 
-keys = dev.new_keys(rows, "cuda")
-def cascade():
-    dev.keys_reset(keys)
-    ws = dev.cascade_fold(x, y, keys, dic, g, 0, dict_terms=terms)
-    return dev.keys_finalize(keys, 2, torch.float32), ws
-l0 = dev.launch_count()
-ms_c, ((ci, cd), _) = timed(cascade, reps)
-launches = (dev.launch_count() - l0) // (reps + 1)
-ms_codes, _ = timed(lambda: dev.hash_codes(x, dic, 0, dict_terms=terms), reps)
+def run(rows=1_000_000, dim=128, reps=5, cpu_rows=2000):
+    """One C5 measurement on the current CUDA device; returns the result dict."""
+    m = int(np.floor(np.log2(rows / 6.)))          # feature.py:364-367
+    n, g = 2, 2
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randint(0, 256, (rows, dim), dtype=torch.uint8, device="cuda", generator=gen)
+    y = torch.randint(0, 256, (rows, dim), dtype=torch.uint8, device="cuda", generator=gen)
+    half = rows // 2
+    src = torch.randint(0, rows, (half,), device="cuda", generator=gen)
+    noise = torch.randint(-3, 4, (half, dim), device="cuda", generator=gen)
+    y[:half] = (x[src].to(torch.int32) + noise).clamp(0, 255).to(torch.uint8)
+    dic = torch.from_numpy(dev.cascade_dictionary(dim, m, n)).cuda()
+    terms = dev.dict_terms_of(dic)   # 0: int8-exact dictionary -> tcgen05 kind::i8 projection
 
-bkeys = dev.new_keys(rows, "cuda")
-def brute():
-    dev.keys_reset(bkeys); dev.l1k2_fold(x, y, bkeys); return dev.keys_finalize(bkeys)
-ms_b, (bi, bd) = timed(brute, 1)
-r1 = float((ci[:, 0] == bi[:, 0]).float().mean()); r2 = float((ci == bi).float().mean())
-r1p = float((ci[:half, 0] == bi[:half, 0]).float().mean())
-out = {"workload": "C5 cascade %d x %d x %d, m=%d n=%d g=%d" % (rows, rows, dim, m, n, g),
-       "cascade_ms": ms_c, "queries_per_s": rows / ms_c * 1e3, "effective_Gpairs_per_s": rows * rows / ms_c / 1e6,
-       "kernels_per_call": int(launches), "hash_codes_ms(x side: image + K2)": ms_codes,
-       "K2_GBps(x side)": rows * (dim + 4 * n) / ms_codes / 1e6,
-       "bruteforce_ms": ms_b, "bruteforce_Gpairs_per_s": rows * rows / ms_b / 1e6, "speedup_vs_bruteforce": ms_b / ms_c,
-       "recall@1_all": r1, "recall@1_planted_half": r1p, "index_agreement_top2": r2}
-if cpu_rows > 0:
-    from oracle import pyoracle as po
-    xf = x.cpu().numpy().astype("float32") - 128
-    yf = y[:cpu_rows].cpu().numpy().astype("float32") - 128
-    cores = os.cpu_count()
-    t0 = time.perf_counter(); oi, od = po.cascade(xf, yf, dic.cpu().numpy(), g, cores); dt = time.perf_counter() - t0
-    out["cpu_port"] = {"cores": cores, "seconds": dt, "queries": cpu_rows, "note": "includes hashing ALL train rows + bucket build; "
-                       "queries_per_s extrapolates only the wall time / queries", "queries_per_s": cpu_rows / dt}
-    out["parity_vs_oracle_rows"] = cpu_rows
-    out["parity_bit_exact"] = bool((ci[:cpu_rows].cpu().numpy().view(np.uint64) == oi).all() and (cd[:cpu_rows].cpu().numpy() == od).all())
-print(json.dumps(out))
+    def timed(fn, reps):
+        fn(); torch.cuda.synchronize()
+        best = 1e30
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+            e0.record(); out = fn(); e1.record(); torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return best, out
+
+    keys = dev.new_keys(rows, "cuda")
+    def cascade():
+        dev.keys_reset(keys)
+        ws = dev.cascade_fold(x, y, keys, dic, g, 0, dict_terms=terms)
+        return dev.keys_finalize(keys, 2, torch.float32), ws
+    l0 = dev.launch_count()
+    ms_c, ((ci, cd), _) = timed(cascade, reps)
+    launches = (dev.launch_count() - l0) // (reps + 1)
+    ms_codes, _ = timed(lambda: dev.hash_codes(x, dic, 0, dict_terms=terms), reps)
+
+    bkeys = dev.new_keys(rows, "cuda")
+    def brute():
+        dev.keys_reset(bkeys); dev.l1k2_fold(x, y, bkeys); return dev.keys_finalize(bkeys)
+    ms_b, (bi, bd) = timed(brute, 1)
+    r1 = float((ci[:, 0] == bi[:, 0]).float().mean()); r2 = float((ci == bi).float().mean())
+    r1p = float((ci[:half, 0] == bi[:half, 0]).float().mean())
+    out = {"workload": "C5 cascade %d x %d x %d, m=%d n=%d g=%d" % (rows, rows, dim, m, n, g),
+           "cascade_ms": ms_c, "queries_per_s": rows / ms_c * 1e3, "effective_Gpairs_per_s": rows * rows / ms_c / 1e6,
+           "kernels_per_call": int(launches), "hash_codes_ms(x side: image + K2)": ms_codes,
+           "K2_GBps(x side)": rows * (dim + 4 * n) / ms_codes / 1e6,
+           "bruteforce_ms": ms_b, "bruteforce_Gpairs_per_s": rows * rows / ms_b / 1e6, "speedup_vs_bruteforce": ms_b / ms_c,
+           "recall@1_all": r1, "recall@1_planted_half": r1p, "index_agreement_top2": r2}
+    if cpu_rows > 0:
+        from oracle import pyoracle as po
+        xf = x.cpu().numpy().astype("float32") - 128
+        yf = y[:cpu_rows].cpu().numpy().astype("float32") - 128
+        cores = os.cpu_count()
+        t0 = time.perf_counter(); oi, od = po.cascade(xf, yf, dic.cpu().numpy(), g, cores); dt = time.perf_counter() - t0
+        out["cpu_port"] = {"cores": cores, "seconds": dt, "queries": cpu_rows, "note": "includes hashing ALL train rows + bucket build; "
+                           "queries_per_s extrapolates only the wall time / queries", "queries_per_s": cpu_rows / dt}
+        out["parity_vs_oracle_rows"] = cpu_rows
+        out["parity_bit_exact"] = bool((ci[:cpu_rows].cpu().numpy().view(np.uint64) == oi).all() and (cd[:cpu_rows].cpu().numpy() == od).all())
+    return out
+
+
+if __name__ == "__main__":
+    a = [int(v) for v in sys.argv[1:5]]
+    d = [1_000_000, 128, 5, 2000]
+    print(json.dumps(run(*(a + d[len(a):]))))
