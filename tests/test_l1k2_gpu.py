@@ -83,3 +83,23 @@ def test_l1k2_large_sampled(po, feature):
     sel = rng.choice(20_000, 256, replace=False)
     oi, od = po.l1k2(x, np.ascontiguousarray(y[sel]), 8)
     assert (gi[sel] == oi).all() and (gd[sel] == od).all()
+
+
+def test_l1k2_concurrent_callers(po, feature):
+    """The reference's entry points are re-entrant (no globals); this library serialises callers on one mutex
+    around its cached device context (SURVEY 8b 'Threading').  Four threads, different inputs, each result exact."""
+    import threading
+    rng = np.random.RandomState(77)
+    jobs = [(_rand(rng, 2000 + 300 * t, 128, 256), _rand(rng, 700 + 100 * t, 128, 256)) for t in range(4)]
+    want = [po.l1k2(x, y, 2) for x, y in jobs]
+    got = [None] * 4
+
+    def work(t):
+        for _ in range(5):
+            got[t] = feature.nn_bruteforcel1k2(*jobs[t])
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    for t in range(4):
+        assert (got[t][0] == want[t][0]).all() and (got[t][1] == want[t][1]).all()
