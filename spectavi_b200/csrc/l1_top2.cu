@@ -29,6 +29,7 @@
 #include "spv_common.h"
 
 #include <cuda.h>
+#include <cstdlib>
 #include <atomic>
 #include <mutex>
 
@@ -56,35 +57,37 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+// try_wait with a suspend-time hint: the hardware parks the warp until the phase flips or the hint (ns) runs
+// out, so a waiting warp issues nothing.  Every issued instruction of a waiting warp -- even the one-lane
+// ISETP / VIADD of a spin counter -- takes a 2-cycle slot of the half-rate ALU pipe the VABSDIFF4 stream is
+// bound by: ncu r01 showed the producer's poll loop (its NANOSLEEP returned after ~12 ns) executing ~2 400
+// warp-instructions per tile on its scheduler.  Parking it is worth 0.25 % (517.4 -> 518.7 G pairs/s).
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(bar), "r"(parity)
+      : "r"(bar), "r"(parity), "r"(hint_ns)
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug must trap, never hang the device.
+// Bounded wait: a protocol bug must trap, never hang the device (2^20 time-outs of 10 us each).
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) {
+  uint32_t timeouts = 0;
+  while (!mbar_try_wait(bar, parity, 10000u)) {
+    if (++timeouts > (1u << 20)) {
       printf("l1_top2: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
       __trap();
     }
   }
 }
-// Producer-side wait: the slot it waits for is microseconds away; back off
-// between polls so the spin does not take issue / ALU slots from the two
-// compute warps that share its scheduler.
+// Producer-side wait: the slot it waits for is microseconds away and the ring is 16 tiles deep
 __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    __nanosleep(128);
-    if (++spins > (1u << 24)) {
+  uint32_t timeouts = 0;
+  while (!mbar_try_wait(bar, parity, 100000u)) {
+    if (++timeouts > (1u << 18)) {
       printf("l1_top2: producer mbarrier wait timed out (block %d)\n", blockIdx.x);
       __trap();
     }
@@ -276,7 +279,7 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
       kload(raA, rbA, y2, x2);
       kload(raB, rbB, y2 + 1, x2 + 1);
       ksad<true>(acc, negthr, raA, rbA);
-#pragma unroll 1
+#pragma unroll 1   // measured: a compile-time trip count or any unrolling here loses 1-20 % (spills / I-cache)
       for (int c = 1; c < nk16; ++c) {     // entering: B holds the second half of chunk c - 1
         kload(raA, rbA, y2 + c * (2 * BY), x2 + c * (2 * BX));
         ksad<false>(acc, negthr, raB, rbB);
@@ -411,9 +414,9 @@ cudaError_t launch_tiled(const CUtensorMap& tmx, const CUtensorMap& tmy, Params 
   if (nst < 2) return cudaErrorInvalidValue;
   p.nst = nst;
   const size_t smem = smem_ytile_bytes(p.nk16) + nst * smem_xstage_bytes(p.nk16) + SMEM_STATE_BYTES + (2 * nst + 2) * 8;
+  const int grid = (int)(p.units < sms ? p.units : sms);
   cudaError_t e = cudaFuncSetAttribute(l1_top2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // per device
   if (e != cudaSuccess) return e;
-  const int grid = (int)(p.units < sms ? p.units : sms);
   l1_top2_kernel<<<grid, NTHREADS, smem, stream>>>(tmx, tmy, p);
   count_launch();
   return cudaGetLastError();
