@@ -176,6 +176,22 @@ __device__ __forceinline__ void ksad(uint32_t (&acc)[TY][TX], const uint32_t (&n
     for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].y, rb[j].y, acc[i][j]);
 }
 
+// the last half-chunk of a tile: each accumulator's sign is folded into its row's sum right behind its final
+// VABSDIFF4, so the 64 IDP.4A ride in the SAD stream instead of forming a dependent tail after it
+__device__ __forceinline__ void ksad_last(uint32_t (&acc)[TY][TX], int (&rs)[TY], const uint2 (&ra)[TY], const uint2 (&rb)[TX]) {
+#pragma unroll
+  for (int i = 0; i < TY; ++i)
+#pragma unroll
+    for (int j = 0; j < TX; ++j) acc[i][j] = sad4(ra[i].x, rb[j].x, acc[i][j]);
+#pragma unroll
+  for (int i = 0; i < TY; ++i)
+#pragma unroll
+    for (int j = 0; j < TX; ++j) {
+      acc[i][j] = sad4(ra[i].y, rb[j].y, acc[i][j]);
+      rs[i] = fold_sign(acc[i][j], rs[i]);
+    }
+}
+
 __global__ void __launch_bounds__(NTHREADS, 1)
 l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmy, const Params p) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -271,6 +287,9 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     }
     mbar_wait(bar_full + 8 * stage, phase);
     const uint4* xs = xs0 + stage * xstage_u4;
+    int rs[TY];   // per query row of the thread tile: < 0 iff some accumulator of the row ended negative
+#pragma unroll
+    for (int i = 0; i < TY; ++i) rs[i] = 0;
     {
       // half-chunk h = 2 c + (0 | 1): the 8-byte halves of chunk c sit at byte offsets 0 and 8 of the 16-byte slots
       const uint2* y2 = reinterpret_cast<const uint2*>(ys);
@@ -286,7 +305,7 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
         kload(raB, rbB, y2 + c * (2 * BY) + 1, x2 + c * (2 * BX) + 1);
         ksad<false>(acc, negthr, raA, rbA);
       }
-      ksad<false>(acc, negthr, raB, rbB);
+      ksad_last(acc, rs, raB, rbB);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(bar_empty + 8 * stage);   // operands are in registers: release the stage
@@ -295,13 +314,6 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     // row of the thread tile (8 independent IDP.4A chains), so that the slow path only visits the rows that
     // tripped: a typical hit is one pair out of the warp's 2 048, and scanning all 64 accumulators of every
     // lane for it cost 3.4 % of the kernel (measured by disabling the slow path)
-    int rs[TY];
-#pragma unroll
-    for (int i = 0; i < TY; ++i) rs[i] = 0;
-#pragma unroll
-    for (int j = 0; j < TX; ++j)
-#pragma unroll
-      for (int i = 0; i < TY; ++i) rs[i] = fold_sign(acc[i][j], rs[i]);
     const int anyneg = (rs[0] | rs[1] | rs[2] | rs[3]) | (rs[4] | rs[5] | rs[6] | rs[7]);
     if (__any_sync(FULL, anyneg < 0)) {
       // slow path (rare): exact (dist, idx) insertion, then tighten the row thresholds
