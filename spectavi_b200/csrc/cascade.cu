@@ -749,6 +749,50 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
     }
     const uint32_t T = __shfl_sync(FULL, inc, 7, 8), excl = inc - len;
     uint32_t done = 0;
+    if (!__any_sync(FULL, (uint32_t)listn + T > (uint32_t)PR_LCAP)) {
+      // common case, the chunk fits every group's list: copy bucket by bucket, the 8 lanes of a group striding
+      // one bucket.  The first 8 ids of all 8 buckets are loaded before any is stored (8 independent loads in
+      // flight); longer buckets (mean occupancy is ~6-8 by the auto-m rule) finish in a short loop.
+      uint32_t b_start[8], b_len[8], b_excl[8];
+      int idv[8];
+#pragma unroll
+      for (int pp = 0; pp < 8; ++pp) {
+        b_start[pp] = __shfl_sync(FULL, start, pp, 8);
+        b_len[pp] = __shfl_sync(FULL, len, pp, 8);
+        b_excl[pp] = __shfl_sync(FULL, excl, pp, 8);
+        idv[pp] = ((uint32_t)l8 < b_len[pp]) ? __ldg(P.ids + b_start[pp] + l8) : -1;
+      }
+#pragma unroll
+      for (int pp = 0; pp < 8; ++pp) {
+        uint32_t s_code = 0;
+        int s_t = 0;
+        if (verify) { s_code = __shfl_sync(FULL, code, pp, 8); s_t = __shfl_sync(FULL, t, pp, 8); }   // warp-uniform branch
+        if ((uint32_t)l8 < b_len[pp]) {
+          int id = idv[pp];
+          if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = -1;
+          list[listn + b_excl[pp] + l8] = id;
+        }
+      }
+      if (__reduce_max_sync(FULL, len) > 8u) {
+#pragma unroll
+        for (int pp = 0; pp < 8; ++pp) {
+          const uint32_t lmax = __reduce_max_sync(FULL, b_len[pp]);
+          uint32_t s_code = 0;
+          int s_t = 0;
+          if (verify) { s_code = __shfl_sync(FULL, code, pp, 8); s_t = __shfl_sync(FULL, t, pp, 8); }
+          for (uint32_t k0 = 8; k0 < lmax; k0 += 8) {
+            const uint32_t k = k0 + l8;
+            if (k < b_len[pp]) {
+              int id = __ldg(P.ids + b_start[pp] + k);
+              if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = -1;
+              list[listn + b_excl[pp] + k] = id;
+            }
+          }
+        }
+      }
+      listn += (int)T;
+      done = T;
+    }
     while (__any_sync(FULL, done < T)) {
       if (__any_sync(FULL, done < T && listn == PR_LCAP)) drain();   // some group is full: all groups drain
       const uint32_t room = (uint32_t)(PR_LCAP - listn), take = (T - done) < room ? (T - done) : room;
