@@ -246,6 +246,28 @@ def side_measurements(device):
     except Exception as ex:                                  # a side measurement must never cost the bench line
         out["c2_castle"] = {"error": repr(ex)[:200]}
     try:
+        # the float matcher on the reference test's shape family (test/test_feature.py:67-81), p = 2, k = 2
+        from spectavi_b200 import feature
+        from oracle import pyoracle as po
+        rng = np.random.RandomState(5)
+        res = {}
+        for rows in (1000, 20000):
+            xf = rng.randn(rows, 132).astype("float32")
+            yf = rng.randn(rows, 132).astype("float32")
+            feature.nn_bruteforce(xf, yf, p=2., mu=0., k=2)
+            best = 1e9
+            for _ in range(3):
+                t0 = time.perf_counter(); fi, fd = feature.nn_bruteforce(xf, yf, p=2., mu=0., k=2); best = min(best, time.perf_counter() - t0)
+            ent = {"ms_e2e": best * 1e3, "Gpairs_per_s_e2e": rows * rows / best / 1e9}
+            if rows == 1000:
+                cfn = po.ref_bruteforce if po.have_ref() else po.bruteforce
+                t0 = time.perf_counter(); oi, od = cfn(xf, yf, 2, 2., 0.); ent["cpu_reference_ms(1 thread: BruteForceNn is single-threaded)"] = (time.perf_counter() - t0) * 1e3
+                ent["idx_equal"] = bool((fi == oi).all()); ent["dist_bit_exact"] = bool((fd.view(np.uint32) == od.view(np.uint32)).all())
+            res["%dx%dx132" % (rows, rows)] = ent
+        out["nn_bruteforce_f32_p2"] = res
+    except Exception as ex:
+        out["nn_bruteforce_f32_p2"] = {"error": repr(ex)[:200]}
+    try:
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import bench_cascade
         out["c5_cascade"] = bench_cascade.run(1_000_000, 128, 3, 1000)
