@@ -599,7 +599,7 @@ __global__ void bucket_scatter_kernel(const int32_t* __restrict__ codes, size_t 
 // ---------------------------------------------------------------- K4
 constexpr int PR_WARPS = 4;      // warps per CTA
 constexpr int PR_QPW = 4;        // query rows per warp (one per 8-lane group)
-constexpr int PR_LCAP = 128;     // candidate ids staged per query before a distance pass (multiple of 8)
+constexpr int PR_LCAP = 256;     // candidate ids staged per query before a distance pass (multiple of 8)
 
 struct PrParams {
   const uint8_t* xu8;            // [xrows][dim]
@@ -644,12 +644,23 @@ __device__ __forceinline__ void top2_merge(unsigned long long& a1, unsigned long
 // rows), so what counts is queries in flight per SM: 4 per warp x 32 warps at 64 registers.
 template <int NCH>
 __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_kernel(const PrParams P) {
+  constexpr int NQ = PR_WARPS * PR_QPW;                 // queries per CTA
+  static_assert(NQ == 16, "the rank computation below takes two slots per lane of an 8-lane group");
   __shared__ __align__(16) int32_t lists[PR_WARPS][PR_QPW][PR_LCAP];
+  __shared__ int Tq[NQ], order[NQ], ovf;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = lane >> 3, l8 = lane & 7;
   const long long first = ((long long)blockIdx.x * PR_WARPS + warp) * PR_QPW;
-  if (first >= P.yrows) return;   // whole warp
-  const bool live = first + q < P.yrows;
-  const int r = live ? (int)(first + q) : P.yrows - 1;   // a dead group shadows the last row and offers nothing
+  const int P_total = P.n << P.nb;   // probe codes of a query: n tables x 2^nb settings
+  // With at most 8 probe codes (one chunk) the whole candidate list of a query is known before the first
+  // gather, and the CTA's 16 lists can be dealt out again by length (below); CTA-uniform.
+  const bool balanced = P_total <= 8;
+  if (!balanced && first >= P.yrows) return;   // whole warp
+  if (balanced) {
+    if (threadIdx.x == 0) ovf = 0;
+    __syncthreads();
+  }
+  bool live = first + q < P.yrows;
+  int r = live ? (int)(first + q) : P.yrows - 1;   // a dead group shadows the last row and offers nothing
   const unsigned FULL = 0xFFFFFFFFu;
   const int nk16 = P.dim / 16;
   const uint32_t mask = (P.mb >= 32) ? 0xFFFFFFFFu : ((1u << P.mb) - 1u);
@@ -721,7 +732,6 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
     listn = 0;
   };
 
-  const int P_total = P.n << P.nb;   // probe codes of a query: n tables x 2^nb settings
   for (int p0 = 0; p0 < P_total; p0 += 8) {
     const int p = p0 + l8;
     uint32_t start = 0, len = 0, code = 0;
@@ -749,6 +759,13 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
     }
     const uint32_t T = __shfl_sync(FULL, inc, 7, 8), excl = inc - len;
     uint32_t done = 0;
+    bool redeal = false;
+    if (balanced) {
+      if (l8 == 0) Tq[warp * PR_QPW + q] = (int)T;
+      if (T > (uint32_t)PR_LCAP) ovf = 1;
+      __syncthreads();
+      redeal = ovf == 0;   // every list of the CTA fits: fill them all, then deal them out by length
+    }
     if (!__any_sync(FULL, (uint32_t)listn + T > (uint32_t)PR_LCAP)) {
       // common case, the chunk fits every group's list: copy bucket by bucket, the 8 lanes of a group striding
       // one bucket.  The first 8 ids of all 8 buckets are loaded before any is stored (8 independent loads in
@@ -792,6 +809,29 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
       }
       listn += (int)T;
       done = T;
+    }
+    if (redeal) {
+      // Load balance: a warp drains in lock step, so its four groups all pay for the longest list (measured:
+      // 16.3 steps per warp where 10.6 would carry the candidates).  Sort the CTA's 16 lists by length and give
+      // warp w the ranks 4w .. 4w+3, so lists of similar length share a warp.
+      __syncthreads();                                  // all 16 lists are complete
+      const int s = warp * PR_QPW + q, Ts = Tq[s];
+      const int ja = l8, jb = l8 + 8;
+      int rank = (Tq[ja] > Ts || (Tq[ja] == Ts && ja < s)) + (Tq[jb] > Ts || (Tq[jb] == Ts && jb < s));
+      rank += __shfl_xor_sync(FULL, rank, 1);
+      rank += __shfl_xor_sync(FULL, rank, 2);
+      rank += __shfl_xor_sync(FULL, rank, 4);
+      if (l8 == 0) order[rank] = s;
+      __syncthreads();
+      const int mine = order[s];                        // the query this group drains
+      list = &lists[0][0][0] + mine * PR_LCAP;
+      listn = Tq[mine];
+      const long long row = (long long)blockIdx.x * NQ + mine;
+      live = row < P.yrows;
+      r = live ? (int)row : P.yrows - 1;
+      const uint4* yr2 = reinterpret_cast<const uint4*>(P.yu8 + (size_t)r * P.dim);
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yr2 + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
     }
     while (__any_sync(FULL, done < T)) {
       if (__any_sync(FULL, done < T && listn == PR_LCAP)) drain();   // some group is full: all groups drain
