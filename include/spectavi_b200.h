@@ -95,6 +95,31 @@ void spv_match_cascading_hash(const float *x, const float *y, int xrows, int yro
  * columns to a multiple of 16.  out: rows x ceil16(dim) float32, bit-identical to the numpy function. */
 void spv_normalize_to_ubyte(const float *x, int rows, int dim, NdArray *out);
 
+/* ---- Part 1c: the second caller of the generic matcher.
+ * spv_nn_bruteforce_filtered replaces BruteForceNn::find_neighbours(out_idx, out_dist, filter_x, filter_y, k)
+ * (src/BruteForceNn.h:37-120), which the reference reaches only from KMedians (it has no C entry point of its
+ * own): the k nearest rows of x, among those named by filter_x, for every row of y named by filter_y, under
+ * sum |d|^p.  The filters are row-id sets (std::unordered_set<size_t> there; lists here, duplicates collapse);
+ * an EMPTY filter means all rows (:45-46).  outidx (yrows x k uint64) / outdist (yrows x k float32) are the
+ * caller's arrays and are IN-OUT as in the reference: only the rows in filter_y are written, and a row with
+ * n < k candidates only gets its last n columns (:111-118).  Distances are bit-exact; candidates that tie in
+ * distance are ordered by row id (the reference's order is its hash set's, i.e. unspecified).
+ *
+ * spv_kmedians_find_nearest_neighbours replaces KMedians::find_nearest_neighbours (src/KMedians.h:260-295), the
+ * body of nn_kmedians after its two clusterings (src/Spectavi.cpp:305-319): x is `other` (train), y is `this`
+ * (query).  For every query cluster g: its c nearest train medians under L1 (:268-273), then the filtered search
+ * (p = 1) of the cluster's rows among the union of those train clusters (:275-293).  All clusters run in one
+ * kernel launch.  The clusterings are inputs -- medians (nm x dim float32) and labels (row -> cluster id) --
+ * because KMedians::run seeds its shuffle from std::random_device (KMedians.h:36-40) and is out of scope
+ * (SURVEY.md 2 row 9).  Outputs are allocated like nn_kmedians' (Spectavi.cpp:310-313). */
+void spv_nn_bruteforce_filtered(const float *x, const float *y, int xrows, int yrows, int dim, int k, float p,
+                                float mu, const uint64_t *filter_x, int nfx, const uint64_t *filter_y, int nfy,
+                                uint64_t *outidx, float *outdist);
+void spv_kmedians_find_nearest_neighbours(const float *x, const float *y, int xrows, int yrows, int dim,
+                                          const float *medians_x, const int32_t *labels_x, int nmx,
+                                          const float *medians_y, const int32_t *labels_y, int nmy, int c, int k,
+                                          NdArray *outidx, NdArray *outdist);
+
 /* ============================ Part 2: device-resident API (device pointers)
  * Results live in a KEY buffer: uint64 keys[2][yrows], key = dist << 32 | idx,
  * all-ones = none; unsigned order of keys == the reference's (dist, idx) rule. */

@@ -65,6 +65,12 @@ def lib():
                                         ct.c_int, ct.c_int, ct.c_int,
                                         ct.c_float, ct.c_float, ct.c_int,
                                         _u64p, ct.c_void_p]
+        L.oracle_bruteforce_filtered.restype = ct.c_int
+        L.oracle_bruteforce_filtered.argtypes = [_f32p, _f32p, ct.c_int,
+                                                 ct.c_int, ct.c_int, ct.c_int,
+                                                 ct.c_float, ct.c_float,
+                                                 _u64p, ct.c_int, _u64p,
+                                                 ct.c_int, _u64p, _f32p]
         L.oracle_hashcodes.restype = ct.c_int
         L.oracle_hashcodes.argtypes = [_f32p, ct.c_int, ct.c_int, _f32p,
                                        ct.c_int, ct.c_int, _i32p]
@@ -107,6 +113,18 @@ def ref():
         R.ref_bruteforce_i32.argtypes = [_i32p, _i32p, ct.c_int, ct.c_int,
                                          ct.c_int, ct.c_int, ct.c_float,
                                          ct.c_float, _u64p, _i32p]
+        R.ref_bruteforce_filtered_f32.restype = ct.c_int
+        R.ref_bruteforce_filtered_f32.argtypes = [_f32p, _f32p, ct.c_int,
+                                                  ct.c_int, ct.c_int, ct.c_int,
+                                                  ct.c_float, ct.c_float,
+                                                  _u64p, ct.c_int, _u64p,
+                                                  ct.c_int, _u64p, _f32p]
+        R.ref_kmedians_nn.restype = ct.c_int
+        R.ref_kmedians_nn.argtypes = [_f32p, _f32p, ct.c_int, ct.c_int,
+                                      ct.c_int, ct.c_int, ct.c_int, ct.c_int,
+                                      ct.c_int, ct.c_uint, _u64p, _f32p,
+                                      _i32p, _i32p, _f32p, _f32p,
+                                      ct.POINTER(ct.c_double)]
         R.ref_cascade.restype = ct.c_int
         R.ref_cascade.argtypes = [_f32p, _f32p, ct.c_int, ct.c_int, ct.c_int,
                                   ct.c_int, ct.c_int, ct.c_int, ct.c_int,
@@ -166,6 +184,51 @@ def bruteforce(x, y, k=2, p=.5, mu=0., use_int=False):
                                  int(use_int), idx, dist.ctypes.data)
     assert rc == 0
     return idx, dist
+
+
+def _flist(f):
+    return np.ascontiguousarray(np.asarray(f, np.uint64).ravel())
+
+
+def bruteforce_filtered(x, y, filter_x, filter_y, k=2, p=1., mu=0., idx=None,
+                        dist=None):
+    """oracle_bruteforce_filtered: BruteForceNn.h:37-120 with explicit filter
+    lists (empty = all rows).  idx / dist are in-out (zeros when omitted)."""
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.ascontiguousarray(y, np.float32)
+    idx = np.zeros((y.shape[0], k), np.uint64) if idx is None else idx
+    dist = np.zeros((y.shape[0], k), np.float32) if dist is None else dist
+    fx, fy = _flist(filter_x), _flist(filter_y)
+    rc = lib().oracle_bruteforce_filtered(x, y, x.shape[0], y.shape[0],
+                                          x.shape[1], k, p, mu, fx, fx.size,
+                                          fy, fy.size, idx, dist)
+    assert rc == 0
+    return idx, dist
+
+
+def kmedians_find_nearest_neighbours(x, y, medians_x, labels_x, medians_y,
+                                     labels_y, c=5, k=2, idx=None, dist=None):
+    """KMedians::find_nearest_neighbours (src/KMedians.h:260-295) given the two
+    clusterings: x = `other` (train side), y = `this` (query side), as
+    nn_kmedians passes them (Spectavi.cpp:318).  For every query cluster: the c
+    nearest train medians under L1 (:268-273), then the filtered brute-force
+    search of the cluster's rows against the union of those train clusters
+    (:275-293), groups in ascending order.  An empty filter means ALL rows to
+    BruteForceNn (BruteForceNn.h:45-46) and that quirk is kept."""
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.ascontiguousarray(y, np.float32)
+    labels_x = np.asarray(labels_x)
+    labels_y = np.asarray(labels_y)
+    nmx, nmy = medians_x.shape[0], medians_y.shape[0]
+    idx = np.zeros((y.shape[0], k), np.uint64) if idx is None else idx
+    dist = np.zeros((y.shape[0], k), np.float32) if dist is None else dist
+    near, _ = bruteforce(medians_x, medians_y, k=c, p=1., mu=0.)
+    xl = [np.flatnonzero(labels_x == g) for g in range(nmx)]
+    for g in range(nmy):
+        fy = np.flatnonzero(labels_y == g)
+        fx = np.concatenate([xl[int(j)] for j in near[g]]) if c else np.zeros(0)
+        bruteforce_filtered(x, y, fx, fy, k, 1., 0., idx, dist)
+    return idx, dist, near
 
 
 def hashcodes(data, dictionary):
@@ -246,6 +309,41 @@ def ref_bruteforce(x, y, k=2, p=.5, mu=0., use_int=False):
         ref().ref_bruteforce_f32(x, y, x.shape[0], y.shape[0], x.shape[1], k,
                                  p, mu, idx, dist)
     return idx, dist
+
+
+def ref_bruteforce_filtered(x, y, filter_x, filter_y, k=2, p=1., mu=0.,
+                            idx=None, dist=None):
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.ascontiguousarray(y, np.float32)
+    idx = np.zeros((y.shape[0], k), np.uint64) if idx is None else idx
+    dist = np.zeros((y.shape[0], k), np.float32) if dist is None else dist
+    fx, fy = _flist(filter_x), _flist(filter_y)
+    ref().ref_bruteforce_filtered_f32(x, y, x.shape[0], y.shape[0], x.shape[1],
+                                      k, p, mu, fx, fx.size, fy, fy.size, idx,
+                                      dist)
+    return idx, dist
+
+
+def ref_kmedians_nn(x, y, nmx, nmy, c=5, k=2, seed=7, want_seconds=False):
+    """The reference's nn_kmedians (Spectavi.cpp:305-319), shuffle seed pinned,
+    plus the clustering it used: (idx, dist, labels_x, labels_y, medians_x,
+    medians_y[, seconds spent in find_nearest_neighbours alone])."""
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.ascontiguousarray(y, np.float32)
+    idx = np.zeros((y.shape[0], k), np.uint64)
+    dist = np.zeros((y.shape[0], k), np.float32)
+    xl = np.full(x.shape[0], -1, np.int32)
+    yl = np.full(y.shape[0], -1, np.int32)
+    xm = np.zeros((nmx, x.shape[1]), np.float32)
+    ym = np.zeros((nmy, x.shape[1]), np.float32)
+    sec = ct.c_double(0.)
+    rc = ref().ref_kmedians_nn(x, y, x.shape[0], y.shape[0], x.shape[1], nmx,
+                               nmy, c, k, seed, idx, dist, xl, yl, xm, ym,
+                               ct.byref(sec))
+    assert rc == 0
+    if want_seconds:
+        return idx, dist, xl, yl, xm, ym, sec.value
+    return idx, dist, xl, yl, xm, ym
 
 
 def ref_cascade(x, y, m, n, g, seed=1234, k=2):

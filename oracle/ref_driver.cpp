@@ -18,6 +18,7 @@
 #include <cstdint>
 #include <cstring>
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <iostream>
 #include <list>
@@ -42,6 +43,7 @@ struct spv_seeded_device {
 #define random_device spv_seeded_device
 #define private public
 #include "CascadingHashNn.h"
+#include "KMedians.h"
 #undef private
 #undef random_device
 
@@ -140,5 +142,57 @@ int ref_cascade_candidates(const float *x, const float *y, int xrows,
   } catch (const std::exception &e) {
     return -1;
   }
+}
+
+// BruteForceNn::find_neighbours(out_idx, out_dist, filter_x, filter_y, k),
+// src/BruteForceNn.h:37-120 -- the overload KMedians drives.  idx / dist are
+// IN-OUT: only the rows named by filter_y are written (all rows when nfy == 0).
+int ref_bruteforce_filtered_f32(const float *x, const float *y, int xrows,
+                                int yrows, int dim, int k, float p, float mu,
+                                const uint64_t *fx, int nfx,
+                                const uint64_t *fy, int nfy, uint64_t *idx,
+                                float *dist) {
+  RowMatrixXsMap _outidx(reinterpret_cast<size_t *>(idx), yrows, k);
+  RowMatrixXfMap _outdist(dist, yrows, k);
+  std::unordered_set<size_t> sx(fx, fx + nfx), sy(fy, fy + nfy);
+  BruteForceNn<> nn(x, y, xrows, yrows, dim, p, mu);
+  nn.find_neighbours(_outidx, _outdist, sx, sy, k);
+  return 0;
+}
+
+// src/Spectavi.cpp:305-319 (nn_kmedians) with the shuffle seed pinned, the
+// reference's y-side row-count slip (:309 passes xrows) kept out by requiring
+// the caller's yrows, and the clustering read back so that the GPU path and the
+// oracle can be given the SAME clusters: labels (m_point_to_median), medians
+// (m_medians), and nothing else.  idx / dist are IN-OUT like above.
+int ref_kmedians_nn(const float *x, const float *y, int xrows, int yrows,
+                    int dim, int nmx, int nmy, int c, int k, unsigned seed,
+                    uint64_t *idx, float *dist, int32_t *xlab, int32_t *ylab,
+                    float *xmed, float *ymed, double *seconds_fnn) {
+  try {
+    g_ref_seed = seed;
+    KMedians<> kmedx(x, xrows, dim, nmx);
+    kmedx.run();
+    g_ref_seed = seed + 1;
+    KMedians<> kmedy(y, yrows, dim, nmy);
+    kmedy.run();
+    RowMatrixXsMap _outidx(reinterpret_cast<size_t *>(idx), yrows, k);
+    RowMatrixXfMap _outdist(dist, yrows, k);
+    auto t0 = std::chrono::steady_clock::now();
+    kmedy.find_nearest_neighbours(kmedx, _outidx, _outdist, c, k);
+    if (seconds_fnn)   // the matching half alone (KMedians.h:260-295), for the CPU baseline
+      *seconds_fnn = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    for (int g = 0; g < nmx; ++g)
+      for (auto &pid : kmedx.m_median_idx[g]) xlab[pid] = g;
+    for (int g = 0; g < nmy; ++g)
+      for (auto &pid : kmedy.m_median_idx[g]) ylab[pid] = g;
+    for (int g = 0; g < nmx; ++g)
+      for (int j = 0; j < dim; ++j) xmed[(size_t)g * dim + j] = kmedx.m_medians(g, j);
+    for (int g = 0; g < nmy; ++g)
+      for (int j = 0; j < dim; ++j) ymed[(size_t)g * dim + j] = kmedy.m_medians(g, j);
+  } catch (const std::exception &e) {
+    return -1;
+  }
+  return 0;
 }
 }

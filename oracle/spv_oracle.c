@@ -245,6 +245,67 @@ int oracle_bruteforce(const void *xv, const void *yv, int xrows, int yrows,
   return 0;
 }
 
+/* BruteForceNn::find_neighbours(out_idx, out_dist, filter_x, filter_y, k),
+ * src/BruteForceNn.h:37-120 -- the overload KMedians::find_nearest_neighbours
+ * drives (src/KMedians.h:260-295).  float32 rows.  The reference walks two
+ * std::unordered_set<size_t>, whose iteration order is unspecified; here the
+ * filters are explicit lists visited in the order given.  The order only
+ * matters when two candidates tie in distance (see the tie note above), so on
+ * tie-free data the output equals the reference's for any order.
+ *   nfx == 0: every train row is a candidate (filter_x.empty(), :46)
+ *   nfy == 0: every query row is processed   (filter_y.empty(), :45)
+ * out_idx / out_dist are IN-OUT: only processed rows are written, and a row
+ * with n < k candidates only gets its last n columns written (:111-118). */
+int oracle_bruteforce_filtered(const float *x, const float *y, int xrows,
+                               int yrows, int dim, int k, float p_in,
+                               float mu, const uint64_t *fx, int nfx,
+                               const uint64_t *fy, int nfy, uint64_t *out_idx,
+                               float *out_dist) {
+  const double p = (double)p_in;
+  if (k < 1) return -1;
+  kpair_t *set = (kpair_t *)malloc(sizeof(kpair_t) * (size_t)(k + 2));
+  if (!set) return -2;
+  const int ylimit = nfy ? nfy : yrows, xlimit = nfx ? nfx : xrows;
+  for (int ir = 0; ir < ylimit; ++ir) {
+    const size_t r = nfy ? (size_t)fy[ir] : (size_t)ir;
+    const float *yr = y + r * dim;
+    int n = 0;
+    double worst = -1;
+    for (int ic = 0; ic < xlimit; ++ic) {
+      const size_t c = nfx ? (size_t)fx[ic] : (size_t)ic;
+      const float *xr = x + c * dim;
+      int pruned = 0;
+      float acc = 0.f;
+      for (int j = 0; j < dim; ++j) {
+        float diff = xr[j] - yr[j];
+        acc += pval_f(diff, p);
+        if (worst >= 0 && (acc + mu * (float)(dim - (j + 1)) > (float)worst)) {
+          pruned = 1;
+          break;
+        }
+      }
+      if (pruned) continue;
+      kpair_t v = {(double)acc, (int)c};
+      if (worst >= 0 && acc < worst) {
+        if (n >= k) --n;
+        n = kset_push(set, n, v);
+        worst = set[n - 1].d;
+      } else if (worst < 0) {
+        n = kset_push(set, n, v);
+        if (n == k) worst = set[n - 1].d;
+      }
+    }
+    for (int q = 0; q < n; ++q) {
+      int col = k - n + q;
+      out_idx[r * k + col] = (uint64_t)set[q].i;
+      out_dist[r * k + col] = (float)set[q].d;
+    }
+  }
+  free(set);
+  (void)xrows;
+  return 0;
+}
+
 /* ---- src/CascadingHashNn.h ---------------------------------------------------
  * The dictionary (generate_hash_dict, :86-100) is an INPUT here: the reference
  * draws it from std::random_device, so no two reference runs agree; tests feed

@@ -226,6 +226,35 @@ void nn_bruteforcei(const int* x, const int* y, int xrows, int yrows, int dim, i
   (void)mu;
   lp_entry("nn_bruteforcei", x, y, true, xrows, yrows, dim, k, p, outidx, outdist);
 }
+// ---- Part 1c: the filter overload of the generic matcher and the caller that drives it
+void spv_nn_bruteforce_filtered(const float* x, const float* y, int xrows, int yrows, int dim, int k, float p, float mu,
+                                const uint64_t* filter_x, int nfx, const uint64_t* filter_y, int nfy, uint64_t* outidx,
+                                float* outdist) {
+  const char* fn = "spv_nn_bruteforce_filtered";
+  (void)mu;
+  if (xrows < 0 || yrows < 0 || dim <= 0 || nfx < 0 || nfy < 0) die(fn, "bad shape %d x %d x %d", xrows, yrows, dim);
+  if (k < 1 || k > LP_MAX_K) die(fn, "k = %d outside [1, %d]", k, LP_MAX_K);
+  if (yrows == 0 || xrows == 0) return;
+  HostCall hc(fn);
+  hc.lpk_filtered(x, y, xrows, yrows, dim, k, (double)p, filter_x, nfx, filter_y, nfy, outidx, outdist);
+}
+
+void spv_kmedians_find_nearest_neighbours(const float* x, const float* y, int xrows, int yrows, int dim,
+                                          const float* medians_x, const int32_t* labels_x, int nmx, const float* medians_y,
+                                          const int32_t* labels_y, int nmy, int c, int k, NdArray* outidx, NdArray* outdist) {
+  const char* fn = "spv_kmedians_find_nearest_neighbours";
+  if (xrows < 0 || yrows < 0 || dim <= 0 || nmx < 1 || nmy < 1) die(fn, "bad shape %d x %d x %d, %d / %d medians", xrows, yrows, dim, nmx, nmy);
+  if (k < 1 || k > LP_MAX_K) die(fn, "k = %d outside [1, %d]", k, LP_MAX_K);
+  // median_idx is nmy x c and only min(c, nmx) columns are ever written there (KMedians.h:271-273)
+  if (c < 1 || c > nmx || c > LP_MAX_K) die(fn, "c = %d outside [1, min(%d medians, %d)]", c, nmx, LP_MAX_K);
+  out_alloc(outidx, (uint64_t)yrows, (uint64_t)k);    // Spectavi.cpp:310-313
+  out_alloc(outdist, (uint64_t)yrows, (uint64_t)k);
+  if (yrows == 0 || xrows == 0) return;
+  HostCall hc(fn);
+  hc.kmedians_nn(x, y, xrows, yrows, dim, medians_x, labels_x, nmx, medians_y, labels_y, nmy, c, k,
+                 reinterpret_cast<uint64_t*>(outidx->m_data), reinterpret_cast<float*>(outdist->m_data));
+}
+
 void nn_cascading_hash(const float* x, const float* y, int xrows, int yrows, int dim, int k, int hash_bit_rate,
                        int num_hash_tables, int num_candidate_neighbours, NdArray* outidx, NdArray* outdist) {
   const char* fn = "nn_cascading_hash";

@@ -1,5 +1,6 @@
 // host_ctx.cu -- see host_ctx.h.
 #include "host_ctx.h"
+#include <algorithm>
 #include "spv_common.h"
 
 #include <dlfcn.h>
@@ -33,7 +34,7 @@ struct Buf {
 struct Gpu {
   int dev = -1;
   cudaStream_t stream = nullptr;
-  Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws, rws;
+  Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws, rws, sel;
 };
 
 struct Nccl {
@@ -355,6 +356,136 @@ void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yro
   CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaStreamSynchronize(D.stream));
+  cudaSetDevice(prev);
+}
+
+// ---- the filter overload and its caller --------------------------------
+// One GPU, like lpk.  filt_begin uploads the rows and the caller's in-out arrays once; filt_run runs
+// any number of groups in ONE launch (their query lists must be disjoint); filt_end downloads.
+void HostCall::filt_begin(const float* x, const float* y, int xrows, int yrows, int dim, int k, const uint64_t* idx,
+                          const float* dist) {
+  Gpu& D = g_rt.gpus[0];
+  CU(fn_, cudaSetDevice(D.dev));
+  const size_t xb = (size_t)xrows * dim * 4, yb = (size_t)yrows * dim * 4;
+  const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
+  CU(fn_, D.x.ensure(xb ? xb : 4));
+  CU(fn_, D.y.ensure(yb ? yb : 4));
+  CU(fn_, D.oidx.ensure(ib ? ib : 8));
+  CU(fn_, D.odist.ensure(db ? db : 4));
+  if (xb) CU(fn_, cudaMemcpyAsync(D.x.p, x, xb, cudaMemcpyHostToDevice, D.stream));
+  if (yb) CU(fn_, cudaMemcpyAsync(D.y.p, y, yb, cudaMemcpyHostToDevice, D.stream));
+  if (ib) CU(fn_, cudaMemcpyAsync(D.oidx.p, idx, ib, cudaMemcpyHostToDevice, D.stream));
+  if (db) CU(fn_, cudaMemcpyAsync(D.odist.p, dist, db, cudaMemcpyHostToDevice, D.stream));
+}
+
+void HostCall::filt_run(const std::vector<FilterGroup>& groups, int xrows, int yrows, int dim, int k, double p) {
+  Gpu& D = g_rt.gpus[0];
+  int sms = 0;
+  CU(fn_, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, D.dev));
+  const int TR = lp_filtered_tile_rows();
+  std::vector<uint32_t> ysel, xsel;
+  std::vector<int4> tiles;
+  int max_xcnt = 0;
+  for (const FilterGroup& g : groups) {
+    const int ypos = (int)ysel.size(), xpos = (int)xsel.size();
+    if (g.ys.empty()) for (int i = 0; i < yrows; ++i) ysel.push_back((uint32_t)i);
+    else ysel.insert(ysel.end(), g.ys.begin(), g.ys.end());
+    if (g.xs.empty()) for (int i = 0; i < xrows; ++i) xsel.push_back((uint32_t)i);
+    else xsel.insert(xsel.end(), g.xs.begin(), g.xs.end());
+    const int ycnt = (int)ysel.size() - ypos, xcnt = (int)xsel.size() - xpos;
+    if (xcnt > max_xcnt) max_xcnt = xcnt;
+    for (int o = 0; o < ycnt; o += TR) tiles.push_back(make_int4(ypos + o, ycnt - o < TR ? ycnt - o : TR, xpos, xcnt));
+  }
+  if (tiles.empty() || max_xcnt == 0) return;
+  if (ysel.size() > 0x7FFFFFFFull || xsel.size() > 0x7FFFFFFFull) die(fn_, "filter lists too long");
+  const size_t yb = ysel.size() * 4, xb = xsel.size() * 4, tb = tiles.size() * sizeof(int4);
+  const size_t yoff = 0, xoff = (yb + 15) / 16 * 16, toff = xoff + (xb + 15) / 16 * 16;
+  CU(fn_, D.sel.ensure(toff + tb));
+  CU(fn_, D.gather.ensure(lp_filtered_partial_bytes((int)tiles.size(), max_xcnt, (int)ysel.size(), k, sms) + 8));
+  char* base = static_cast<char*>(D.sel.p);
+  CU(fn_, cudaMemcpyAsync(base + yoff, ysel.data(), yb, cudaMemcpyHostToDevice, D.stream));
+  CU(fn_, cudaMemcpyAsync(base + xoff, xsel.data(), xb, cudaMemcpyHostToDevice, D.stream));
+  CU(fn_, cudaMemcpyAsync(base + toff, tiles.data(), tb, cudaMemcpyHostToDevice, D.stream));
+  CU(fn_, lp_topk_filtered((const float*)D.x.p, (const float*)D.y.p, dim, k, p, (const int4*)(base + toff), (int)tiles.size(),
+                           (const uint32_t*)(base + yoff), (int)ysel.size(), (const uint32_t*)(base + xoff), max_xcnt,
+                           (unsigned long long*)D.gather.p, (uint64_t*)D.oidx.p, (float*)D.odist.p, D.stream));
+  CU(fn_, cudaStreamSynchronize(D.stream));   // the host vectors above are about to go away
+}
+
+void HostCall::filt_end(int yrows, int k, uint64_t* idx, float* dist) {
+  Gpu& D = g_rt.gpus[0];
+  const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
+  if (ib) CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
+  if (db) CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
+  CU(fn_, cudaStreamSynchronize(D.stream));
+}
+
+// a std::unordered_set<size_t> built from a list: duplicates collapse; ascending order here
+static std::vector<uint32_t> as_set(const char* fn, const uint64_t* f, int n, int rows, const char* what) {
+  std::vector<uint32_t> v;
+  v.reserve(n > 0 ? n : 0);
+  for (int i = 0; i < n; ++i) {
+    if (f[i] >= (uint64_t)rows) die(fn, "%s[%d] = %llu is not a row (< %d)", what, i, (unsigned long long)f[i], rows);
+    v.push_back((uint32_t)f[i]);
+  }
+  std::sort(v.begin(), v.end());
+  v.erase(std::unique(v.begin(), v.end()), v.end());
+  return v;
+}
+
+void HostCall::lpk_filtered(const float* x, const float* y, int xrows, int yrows, int dim, int k, double p,
+                            const uint64_t* filter_x, int nfx, const uint64_t* filter_y, int nfy, uint64_t* idx, float* dist) {
+  int prev = 0;
+  cudaGetDevice(&prev);
+  std::vector<FilterGroup> groups(1);
+  groups[0].xs = as_set(fn_, filter_x, nfx, xrows, "filter_x");
+  groups[0].ys = as_set(fn_, filter_y, nfy, yrows, "filter_y");
+  filt_begin(x, y, xrows, yrows, dim, k, idx, dist);
+  filt_run(groups, xrows, yrows, dim, k, p);
+  filt_end(yrows, k, idx, dist);
+  cudaSetDevice(prev);
+}
+
+void HostCall::kmedians_nn(const float* x, const float* y, int xrows, int yrows, int dim, const float* medians_x,
+                           const int32_t* labels_x, int nmx, const float* medians_y, const int32_t* labels_y, int nmy, int c,
+                           int k, uint64_t* idx, float* dist) {
+  int prev = 0;
+  cudaGetDevice(&prev);
+  // KMedians.h:268-273: the c nearest `other` medians of every median, L1 (K1f on the GPU, exact)
+  std::vector<uint64_t> near((size_t)nmy * c);
+  std::vector<float> near_d((size_t)nmy * c);
+  lpk(medians_x, medians_y, false, nmx, nmy, dim, c, 1.0, near.data(), near_d.data());
+  // cluster member lists (m_median_idx), ascending row id
+  std::vector<std::vector<uint32_t>> xl(nmx), yl(nmy);
+  for (int i = 0; i < xrows; ++i) {
+    if (labels_x[i] < 0 || labels_x[i] >= nmx) die(fn_, "labels_x[%d] = %d outside [0, %d)", i, labels_x[i], nmx);
+    xl[labels_x[i]].push_back((uint32_t)i);
+  }
+  for (int i = 0; i < yrows; ++i) {
+    if (labels_y[i] < 0 || labels_y[i] >= nmy) die(fn_, "labels_y[%d] = %d outside [0, %d)", i, labels_y[i], nmy);
+    yl[labels_y[i]].push_back((uint32_t)i);
+  }
+  filt_begin(x, y, xrows, yrows, dim, k, idx, dist);
+  // KMedians.h:275-293, one filtered search per query cluster, in cluster order.  Clusters are disjoint, so a run of
+  // groups is ONE launch; a group whose query list or candidate union is empty means "all rows" to BruteForceNn
+  // (BruteForceNn.h:45-46) and overlaps the others, so it is launched on its own, in sequence, like the reference.
+  std::vector<FilterGroup> batch;
+  for (int g = 0; g < nmy; ++g) {
+    FilterGroup fg;
+    fg.ys = yl[g];
+    for (int j = 0; j < c; ++j) {
+      const std::vector<uint32_t>& m = xl[near[(size_t)g * c + j]];
+      fg.xs.insert(fg.xs.end(), m.begin(), m.end());
+    }
+    if (fg.ys.empty() || fg.xs.empty()) {
+      if (!batch.empty()) { filt_run(batch, xrows, yrows, dim, k, 1.0); batch.clear(); }
+      filt_run(std::vector<FilterGroup>(1, fg), xrows, yrows, dim, k, 1.0);
+    } else {
+      batch.push_back(std::move(fg));
+    }
+  }
+  if (!batch.empty()) filt_run(batch, xrows, yrows, dim, k, 1.0);
+  filt_end(yrows, k, idx, dist);
   cudaSetDevice(prev);
 }
 

@@ -12,6 +12,7 @@
 #include <cstdint>
 #include <functional>
 #include <mutex>
+#include <vector>
 
 namespace spv {
 
@@ -44,6 +45,14 @@ class HostCall {
   // brute-force sum |x-y|^p top-k over float32 / int32 rows (yrows x k out)
   void lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p, uint64_t* idx,
            void* dist);
+  // The filter overload of the generic matcher (BruteForceNn.h:37-49).  filter_x / filter_y: row-id sets, empty = all
+  // rows.  idx / dist (yrows x k) are in-out: only rows in filter_y are written.
+  void lpk_filtered(const float* x, const float* y, int xrows, int yrows, int dim, int k, double p,
+                    const uint64_t* filter_x, int nfx, const uint64_t* filter_y, int nfy, uint64_t* idx, float* dist);
+  // KMedians::find_nearest_neighbours (KMedians.h:260-295) given both clusterings: x = `other`, y = `this`.
+  void kmedians_nn(const float* x, const float* y, int xrows, int yrows, int dim, const float* medians_x,
+                   const int32_t* labels_x, int nmx, const float* medians_y, const int32_t* labels_y, int nmy, int c, int k,
+                   uint64_t* idx, float* dist);
   // cascade-of-hashes matcher, float32 rows holding integers in [-128, 127] (yrows x kcols out)
   void cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
                uint64_t* idx, float* dist, const MatchSink* ms = nullptr);
@@ -52,6 +61,10 @@ class HostCall {
   void normalize(const float* x, int rows, int dim, float* out);
 
  private:
+  struct FilterGroup { std::vector<uint32_t> ys, xs; };   // empty list = all rows (BruteForceNn.h:45-46)
+  void filt_begin(const float* x, const float* y, int xrows, int yrows, int dim, int k, const uint64_t* idx, const float* dist);
+  void filt_run(const std::vector<FilterGroup>& groups, int xrows, int yrows, int dim, int k, double p);
+  void filt_end(int yrows, int k, uint64_t* idx, float* dist);
   void deliver_matches(const MatchSink& ms, int yrows, bool dist_f32);   // K6 on GPU 0's merged keys
   const char* fn_;
   std::unique_lock<std::mutex> lock_;

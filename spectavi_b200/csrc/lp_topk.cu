@@ -21,6 +21,13 @@
 // result; mu != 0 (an approximation knob) is accepted and computed exactly.
 //
 // Bound: FP32 CUDA-core pipe, 2 (p=1) or 3 (p=2) dependent-free ops per element.
+//
+// FILT = true is the filter overload (BruteForceNn.h:37-49: unordered_set filter_x /
+// filter_y), in the batched form its one caller needs (KMedians::find_nearest_neighbours,
+// src/KMedians.h:260-295: one filtered search per query cluster): every CTA takes a tile
+// {ypos, ycnt, xpos, xcnt} -- up to 128 query rows named by ysel[ypos ..) against the
+// candidate rows named by xsel[xpos .. xpos + xcnt) -- so ALL clusters run in one launch.
+// Rows are gathered through the lists while staging; keys carry the real train row id.
 #include "spv_common.h"
 
 #include <cstdint>
@@ -54,13 +61,18 @@ struct LpParams {
   int nxt;                         // train tiles in total
   int splits;                      // train-side splits (gridDim.y)
   unsigned long long* partial;     // [splits][yrows][k] sorted keys, KEY_NONE padded
+  // FILT only
+  const uint32_t* ysel;            // query row ids, group after group
+  const uint32_t* xsel;            // candidate row ids, group after group
+  const int4* tiles;               // per blockIdx.x: {ypos, ycnt <= TB, xpos, xcnt}
+  int nysel;                       // entries in ysel (row stride of partial)
 };
 
 // key = order-preserving 32 bits of the distance << 32 | train index
 __device__ __forceinline__ uint32_t dist_bits(float d) { return __float_as_uint(d); }   // d >= 0
 __device__ __forceinline__ uint32_t dist_bits(int d) { return (uint32_t)d; }            // d >= 0
 
-template <typename T, int PM>
+template <typename T, int PM, bool FILT>
 __global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* ys = reinterpret_cast<T*>(smem_raw);                     // [KC][PITCH]
@@ -70,22 +82,39 @@ __global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
   unsigned long long* qkey = reinterpret_cast<unsigned long long*>(cnt + TB);   // [QCAP]
   unsigned short* qrow = reinterpret_cast<unsigned short*>(qkey + QCAP);        // [QCAP]
   int* qn = reinterpret_cast<int*>(qrow + QCAP);              // [4]
-  unsigned long long* list = reinterpret_cast<unsigned long long*>(qn + 4);     // [TB][k] ascending
+  uint32_t* yid = reinterpret_cast<uint32_t*>(qn + 4);        // [TB] FILT: query row ids of this tile
+  uint32_t* xid = yid + TB;                                   // [TB] FILT: train row ids of the current train tile
+  unsigned long long* list = reinterpret_cast<unsigned long long*>(xid + TB);   // [TB][k] ascending
 
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   const int k = P.k, dim = P.dim;
-  const int y0 = blockIdx.x * TB;
+  int y0, ycnt, xbase, xcnt, nxt, prow;   // prow: row stride of P.partial
+  if (FILT) {
+    const int4 tl = P.tiles[blockIdx.x];
+    y0 = tl.x; ycnt = tl.y; xbase = tl.z; xcnt = tl.w;
+    nxt = (xcnt + TB - 1) / TB; prow = P.nysel;
+  } else {
+    y0 = blockIdx.x * TB; ycnt = min(TB, P.yrows - y0); xbase = 0; xcnt = P.xrows;
+    nxt = P.nxt; prow = P.yrows;
+  }
   const T* __restrict__ gx = reinterpret_cast<const T*>(P.x);
   const T* __restrict__ gy = reinterpret_cast<const T*>(P.y);
   // contiguous range of train tiles of this split, scanned in ascending order
-  const int t0 = (int)((long long)P.nxt * blockIdx.y / P.splits);
-  const int t1 = (int)((long long)P.nxt * (blockIdx.y + 1) / P.splits);
+  const int t0 = (int)((long long)nxt * blockIdx.y / P.splits);
+  const int t1 = (int)((long long)nxt * (blockIdx.y + 1) / P.splits);
 
-  if (tid < TB) { thr[tid] = THR_NONE; cnt[tid] = 0; }
+  if (tid < TB) {
+    thr[tid] = THR_NONE; cnt[tid] = 0;
+    if (FILT) yid[tid] = tid < ycnt ? P.ysel[y0 + tid] : 0u;
+  }
   __syncthreads();
 
   for (int t = t0; t < t1; ++t) {
     const int x0 = t * TB;
+    if (FILT) {   // the previous tile's last reader of xid is behind the __syncthreads_or that ended its selection
+      if (tid < TB) xid[tid] = x0 + tid < xcnt ? P.xsel[xbase + x0 + tid] : 0u;
+      __syncthreads();
+    }
     T acc[8][8];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
@@ -99,8 +128,8 @@ __global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
         const int e = tid + NT * q, col = e % KC, row = e / KC;
         const bool cok = c0 + col < dim;
         T yv = (T)0, xv = (T)0;
-        if (cok && y0 + row < P.yrows) yv = gy[(size_t)(y0 + row) * dim + c0 + col];
-        if (cok && x0 + row < P.xrows) xv = gx[(size_t)(x0 + row) * dim + c0 + col];
+        if (cok && row < ycnt) yv = gy[(size_t)(FILT ? yid[row] : (uint32_t)(y0 + row)) * dim + c0 + col];
+        if (cok && x0 + row < xcnt) xv = gx[(size_t)(FILT ? xid[row] : (uint32_t)(x0 + row)) * dim + c0 + col];
         ys[col * PITCH + row] = yv;
         xs[col * PITCH + row] = xv;
       }
@@ -130,32 +159,69 @@ __global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
       __syncthreads();
     }
 
-    // ---- selection: candidates (dist < row's k-th best so far) go through a queue
+    // ---- selection: candidates (dist <= the row's k-th best so far; the row owner compares whole keys)
+    // go through a queue.  On a CTA's first train tile no row has a k-th best yet and all 128 x 128
+    // pairs would queue up; instead each half-warp (the 16 threads sharing a row) first derives a bound:
+    // the k-th smallest of its 16 per-thread minima is >= the row's k-th smallest distance.
+    uint32_t thb[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) thb[i] = thr[ty * 8 + i];
+    if (t == t0 && k <= 16) {
+      const int lane = tid & 31, hb = lane & 16;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint32_t mn = THR_NONE;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (x0 + tx * 8 + j < xcnt) mn = min(mn, dist_bits(acc[i][j]));
+        int rank = 0;
+#pragma unroll
+        for (int o = 0; o < 16; ++o) {
+          const uint32_t v = __shfl_sync(0xFFFFFFFFu, mn, hb | o);
+          rank += (v < mn) || (v == mn && o < tx);
+        }
+        const unsigned has = (__ballot_sync(0xFFFFFFFFu, rank == k - 1) >> hb) & 0xFFFFu;   // exactly one lane
+        const uint32_t bound = __shfl_sync(0xFFFFFFFFu, mn, hb | (__ffs(has) - 1));
+        if (thb[i] == THR_NONE) thb[i] = bound;     // THR_NONE again when fewer than k threads hold a valid pair
+      }
+    }
     unsigned long long pend = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const uint32_t th = thr[ty * 8 + i];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const bool c = (x0 + tx * 8 + j < P.xrows) && (th == THR_NONE || dist_bits(acc[i][j]) < th);
+        const bool c = (x0 + tx * 8 + j < xcnt) && dist_bits(acc[i][j]) <= thb[i];   // THR_NONE admits all
         pend |= (unsigned long long)c << (i * 8 + j);
       }
     }
     while (__syncthreads_or(pend != 0)) {
       if (tid == 0) qn[0] = 0;
       __syncthreads();
+      {   // one queue reservation per warp
+        const int lane = tid & 31, mine = __popcll(pend);
+        int incl = mine;
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+        for (int o = 1; o < 32; o <<= 1) {
+          const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        int base = 0;
+        if (lane == 31 && incl) base = atomicAdd(&qn[0], incl);
+        int slot = __shfl_sync(0xFFFFFFFFu, base, 31) + incl - mine;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if ((pend >> (i * 8 + j)) & 1) {
-            const int slot = atomicAdd(&qn[0], 1);
-            if (slot < QCAP) {
-              qkey[slot] = ((unsigned long long)dist_bits(acc[i][j]) << 32) | (uint32_t)(x0 + tx * 8 + j);
-              qrow[slot] = (unsigned short)(ty * 8 + i);
-              pend &= ~(1ull << (i * 8 + j));
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if ((pend >> (i * 8 + j)) & 1) {
+              if (slot < QCAP) {
+                qkey[slot] = ((unsigned long long)dist_bits(acc[i][j]) << 32) |
+                             (FILT ? xid[tx * 8 + j] : (uint32_t)(x0 + tx * 8 + j));
+                qrow[slot] = (unsigned short)(ty * 8 + i);
+                pend &= ~(1ull << (i * 8 + j));
+              }
+              ++slot;
             }
-          }
+      }
       __syncthreads();
       const int n = min(qn[0], QCAP);
       if (tid < TB) {               // thread r owns row r's list
@@ -184,15 +250,15 @@ __global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
           const uint32_t th = thr[ty * 8 + i];
 #pragma unroll
           for (int j = 0; j < 8; ++j)
-            if (((pend >> (i * 8 + j)) & 1) && th != THR_NONE && !(dist_bits(acc[i][j]) < th)) pend &= ~(1ull << (i * 8 + j));
+            if (((pend >> (i * 8 + j)) & 1) && dist_bits(acc[i][j]) > th) pend &= ~(1ull << (i * 8 + j));
         }
       }
     }
   }
 
   // publish this split's sorted lists
-  if (tid < TB && y0 + tid < P.yrows) {
-    unsigned long long* out = P.partial + ((size_t)blockIdx.y * P.yrows + y0 + tid) * k;
+  if (tid < TB && tid < ycnt) {
+    unsigned long long* out = P.partial + ((size_t)blockIdx.y * prow + y0 + tid) * k;
     const int m = cnt[tid];
     for (int q = 0; q < k; ++q) out[q] = q < m ? list[(size_t)tid * k + q] : KEY_NONE;
   }
@@ -202,11 +268,15 @@ __global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
 // reference's layout: ascending, RIGHT-aligned when fewer than k exist
 // (BruteForceNn.h:111-118 fills from column k-1 downwards; the columns before
 // keep the caller's zeros)
+// ysel != nullptr (filtered): list position `row` belongs to output row ysel[row]; a row's unfilled
+// leading columns and every row outside the filter keep the caller's values (idx / dist are in-out).
 template <typename D>
 __global__ void lp_merge_kernel(const unsigned long long* __restrict__ partial, int splits, int yrows, int k,
-                                uint64_t* __restrict__ idx, D* __restrict__ dist) {
+                                uint64_t* __restrict__ idx, D* __restrict__ dist,
+                                const uint32_t* __restrict__ ysel = nullptr) {
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= yrows) return;
+  const size_t orow = ysel ? ysel[row] : (uint32_t)row;
   // count what exists (at most k are needed)
   int total = 0;
   for (int s = 0; s < splits && total < k; ++s) {
@@ -231,32 +301,32 @@ __global__ void lp_merge_kernel(const unsigned long long* __restrict__ partial, 
     }
     last = best; have_last = true;
     const int col = k - n + out;
-    idx[(size_t)row * k + col] = best & 0xFFFFFFFFull;
+    idx[orow * k + col] = best & 0xFFFFFFFFull;
     const uint32_t b = (uint32_t)(best >> 32);
-    if constexpr (std::is_same<D, float>::value) dist[(size_t)row * k + col] = __uint_as_float(b);
-    else dist[(size_t)row * k + col] = (int32_t)b;
+    if constexpr (std::is_same<D, float>::value) dist[orow * k + col] = __uint_as_float(b);
+    else dist[orow * k + col] = (int32_t)b;
   }
 }
 
 size_t lp_smem_bytes(int k) {
-  return (size_t)2 * KC * PITCH * 4 + TB * 4 + TB * 4 + QCAP * 8 + QCAP * 2 + 16 + (size_t)TB * k * 8;
+  return (size_t)2 * KC * PITCH * 4 + TB * 4 + TB * 4 + QCAP * 8 + QCAP * 2 + 16 + 2 * TB * 4 + (size_t)TB * k * 8;
 }
 
-template <typename T, int PM>
+template <typename T, int PM, bool FILT>
 cudaError_t launch_lp(const LpParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
-  cudaError_t e = cudaFuncSetAttribute(lp_topk_kernel<T, PM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(lp_topk_kernel<T, PM, FILT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  lp_topk_kernel<T, PM><<<grid, NT, smem, stream>>>(P);
+  lp_topk_kernel<T, PM, FILT><<<grid, NT, smem, stream>>>(P);
   count_launch();
   return cudaGetLastError();
 }
 
-template <typename T>
+template <typename T, bool FILT = false>
 cudaError_t launch_lp_p(const LpParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
-  if (P.p == 1.0) return launch_lp<T, P_ONE>(P, grid, smem, stream);     // BruteForceNn.h:70-78: exact comparisons on m_p
-  if (P.p == 2.0) return launch_lp<T, P_TWO>(P, grid, smem, stream);
-  if (P.p == 0.5) return launch_lp<T, P_HALF>(P, grid, smem, stream);
-  return launch_lp<T, P_POW>(P, grid, smem, stream);
+  if (P.p == 1.0) return launch_lp<T, P_ONE, FILT>(P, grid, smem, stream);     // BruteForceNn.h:70-78: exact comparisons on m_p
+  if (P.p == 2.0) return launch_lp<T, P_TWO, FILT>(P, grid, smem, stream);
+  if (P.p == 0.5) return launch_lp<T, P_HALF, FILT>(P, grid, smem, stream);
+  return launch_lp<T, P_POW, FILT>(P, grid, smem, stream);
 }
 
 }  // namespace
@@ -289,12 +359,49 @@ cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int 
   P.nxt = (xrows + TB - 1) / TB;
   P.splits = lp_splits(xrows, yrows, sms);
   P.partial = partial;
+  P.ysel = P.xsel = nullptr; P.tiles = nullptr; P.nysel = 0;
   const dim3 grid((yrows + TB - 1) / TB, P.splits);
   const size_t smem = lp_smem_bytes(k);
   e = is_int ? launch_lp_p<int>(P, grid, smem, stream) : launch_lp_p<float>(P, grid, smem, stream);
   if (e != cudaSuccess) return e;
   if (is_int) lp_merge_kernel<int32_t><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (int32_t*)ddist);
   else lp_merge_kernel<float><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (float*)ddist);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---- the filter overload, batched over groups (see the header)
+int lp_filtered_tile_rows() { return TB; }
+
+int lp_filtered_splits(int ntiles, int max_xcnt, int sms) {
+  if (ntiles < 1) return 1;
+  const int nxt = (max_xcnt + TB - 1) / TB;
+  int s = (2 * sms + ntiles - 1) / ntiles;
+  if (s > nxt) s = nxt;
+  return s < 1 ? 1 : s;
+}
+
+size_t lp_filtered_partial_bytes(int ntiles, int max_xcnt, int nysel, int k, int sms) {
+  return (size_t)lp_filtered_splits(ntiles, max_xcnt, sms) * (size_t)nysel * k * sizeof(unsigned long long);
+}
+
+cudaError_t lp_topk_filtered(const float* dx, const float* dy, int dim, int k, double p, const int4* dtiles, int ntiles,
+                             const uint32_t* dysel, int nysel, const uint32_t* dxsel, int max_xcnt,
+                             unsigned long long* partial, uint64_t* didx, float* ddist, cudaStream_t stream) {
+  if (ntiles <= 0 || nysel <= 0) return cudaSuccess;
+  if (k < 1 || k > LP_MAX_K || dim < 1) return cudaErrorInvalidValue;
+  int dev = 0, sms = 0;
+  cudaError_t e;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  LpParams P;
+  P.x = dx; P.y = dy; P.xrows = 0; P.yrows = 0; P.dim = dim; P.k = k; P.p = p; P.nxt = 0;
+  P.splits = lp_filtered_splits(ntiles, max_xcnt, sms);
+  P.partial = partial;
+  P.ysel = dysel; P.xsel = dxsel; P.tiles = dtiles; P.nysel = nysel;
+  const dim3 grid(ntiles, P.splits);
+  if ((e = launch_lp_p<float, true>(P, grid, lp_smem_bytes(k), stream)) != cudaSuccess) return e;
+  lp_merge_kernel<float><<<(nysel + 127) / 128, 128, 0, stream>>>(partial, P.splits, nysel, k, didx, ddist, dysel);
   count_launch();
   return cudaGetLastError();
 }

@@ -50,6 +50,14 @@ constexpr int LP_MAX_K = 128;
 size_t lp_partial_bytes(int xrows, int yrows, int k, int sms);
 cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
                     unsigned long long* partial, uint64_t* didx, void* ddist, cudaStream_t stream);
+// The filter overload (BruteForceNn.h:37-49), batched: tile t = {ypos, ycnt <= lp_filtered_tile_rows(), xpos, xcnt}
+// searches query rows ysel[ypos .. ypos+ycnt) among train rows xsel[xpos .. xpos+xcnt).  A query row id may appear
+// in ysel once.  didx / ddist (yrows x k) are in-out: only rows named by ysel are written, right-aligned.
+int lp_filtered_tile_rows();
+size_t lp_filtered_partial_bytes(int ntiles, int max_xcnt, int nysel, int k, int sms);
+cudaError_t lp_topk_filtered(const float* dx, const float* dy, int dim, int k, double p, const int4* dtiles, int ntiles,
+                             const uint32_t* dysel, int nysel, const uint32_t* dxsel, int max_xcnt,
+                             unsigned long long* partial, uint64_t* didx, float* ddist, cudaStream_t stream);
 // ---- cascade.cu : the cascade-of-hashes matcher (CascadingHashNn.h)
 // rows are uint8 (value + 128); ddict: [n][dim][m] fp32 on the device; dict_terms 1
 // when every entry is exact in bf16 (the library's own quantised dictionary), else 3.

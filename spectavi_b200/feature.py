@@ -65,6 +65,28 @@ _normalize.restype = None
 _normalize.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"), ct.c_int, ct.c_int, ct.POINTER(NdArray)]
 
 
+_u64list = ndpointer(ct.c_uint64, flags="C_CONTIGUOUS")
+_nn_filtered = clib.spv_nn_bruteforce_filtered
+_nn_filtered.restype = None
+_nn_filtered.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                         ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                         ct.c_int, ct.c_int, ct.c_int, ct.c_int, ct.c_float, ct.c_float,
+                         _u64list, ct.c_int, _u64list, ct.c_int,
+                         ndpointer(ct.c_uint64, flags="C_CONTIGUOUS"),
+                         ndpointer(ct.c_float, flags="C_CONTIGUOUS")]
+
+_kmedians_fnn = clib.spv_kmedians_find_nearest_neighbours
+_kmedians_fnn.restype = None
+_kmedians_fnn.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                          ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                          ct.c_int, ct.c_int, ct.c_int,
+                          ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                          ndpointer(ct.c_int32, flags="C_CONTIGUOUS"), ct.c_int,
+                          ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
+                          ndpointer(ct.c_int32, flags="C_CONTIGUOUS"), ct.c_int,
+                          ct.c_int, ct.c_int, ct.POINTER(NdArray), ct.POINTER(NdArray)]
+
+
 def nn_bruteforce(x, y, p=.5, mu=0., k=2, use_int=False):
     """k nearest rows of ``x`` for every row of ``y`` under sum |d|^p
     (reference feature.py:246-289).  Returns ``(idx uint64, dist)`` of shape
@@ -83,6 +105,52 @@ def nn_bruteforce(x, y, p=.5, mu=0., k=2, use_int=False):
         xi = np.round(100 * x).astype('int32')
         yi = np.round(100 * y).astype('int32')
         _nn_bruteforcei(xi, yi, xrows, yrows, dim, k, p, mu, nn_idx, nn_dist)
+    return nn_idx.asarray(), nn_dist.asarray()
+
+
+def nn_bruteforce_filtered(x, y, filter_x, filter_y, p=1., mu=0., k=2, nn_idx=None, nn_dist=None):
+    """``BruteForceNn::find_neighbours(out_idx, out_dist, filter_x, filter_y, k)``
+    (reference src/BruteForceNn.h:37-120): k nearest rows of ``x`` among
+    ``filter_x`` for every row of ``y`` in ``filter_y``; an empty filter means all
+    rows.  ``nn_idx`` / ``nn_dist`` (yrows x k) are updated in place on the rows of
+    ``filter_y`` (zeros are allocated when omitted) and returned."""
+    xrows, dim = x.shape
+    yrows, ydim = y.shape
+    assert ydim == dim
+    if nn_idx is None:
+        nn_idx = np.zeros((yrows, k), 'uint64')
+    if nn_dist is None:
+        nn_dist = np.zeros((yrows, k), 'float32')
+    assert nn_idx.shape == (yrows, k) and nn_dist.shape == (yrows, k)
+    fx = np.ascontiguousarray(np.asarray(filter_x, 'uint64').ravel())
+    fy = np.ascontiguousarray(np.asarray(filter_y, 'uint64').ravel())
+    if (fx.size and fx.max() >= xrows) or (fy.size and fy.max() >= yrows):
+        raise ValueError("filter holds a row id outside the matrix")   # the C entry point aborts on this
+    _nn_filtered(x, y, xrows, yrows, dim, k, p, mu, fx, fx.size, fy, fy.size, nn_idx, nn_dist)
+    return nn_idx, nn_dist
+
+
+def kmedians_find_nearest_neighbours(x, y, medians_x, labels_x, medians_y, labels_y, c=5, k=2):
+    """``KMedians::find_nearest_neighbours`` (reference src/KMedians.h:260-295),
+    the matching half of ``nn_kmedians`` (feature.py:328-337), given both
+    clusterings: for every cluster of ``y`` the ``c`` nearest medians of ``x``
+    (L1), then the k nearest rows (L1) of each of its rows among the members of
+    those clusters.  ``labels_*``: cluster id of every row; ``medians_*``:
+    (clusters, dim) float32.  Returns ``(idx uint64, dist float32)``, (yrows, k)."""
+    xrows, dim = x.shape
+    yrows, ydim = y.shape
+    assert ydim == dim and medians_x.shape[1] == dim and medians_y.shape[1] == dim
+    lx = np.ascontiguousarray(labels_x, 'int32')
+    ly = np.ascontiguousarray(labels_y, 'int32')
+    assert lx.shape == (xrows,) and ly.shape == (yrows,)
+    if lx.min() < 0 or lx.max() >= medians_x.shape[0] or ly.min() < 0 or ly.max() >= medians_y.shape[0]:
+        raise ValueError("label outside [0, number of medians)")           # the C entry point aborts on this
+    if not 1 <= c <= medians_x.shape[0]:
+        raise ValueError("c must be in [1, number of train medians]")
+    nn_idx = NdArray(dtype='uint64')
+    nn_dist = NdArray(dtype='float32')
+    _kmedians_fnn(x, y, xrows, yrows, dim, np.ascontiguousarray(medians_x, 'float32'), lx, medians_x.shape[0],
+                  np.ascontiguousarray(medians_y, 'float32'), ly, medians_y.shape[0], c, k, nn_idx, nn_dist)
     return nn_idx.asarray(), nn_dist.asarray()
 
 
