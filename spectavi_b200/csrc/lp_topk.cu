@@ -121,20 +121,32 @@ __global__ void __launch_bounds__(NT, 1) lp_topk_kernel(const LpParams P) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[i][j] = (T)0;
 
-    for (int c0 = 0; c0 < dim; c0 += KC) {
-      // stage KC columns of both tiles, transposed to [column][row]
+    // KC columns of both tiles per step, transposed to [column][row] in shared memory; the next step's
+    // global loads are issued into registers before this step's arithmetic and land behind it
+    T py[(TB * KC) / NT], px[(TB * KC) / NT];
+    auto fetch = [&](int c0) {
 #pragma unroll
       for (int q = 0; q < (TB * KC) / NT; ++q) {
         const int e = tid + NT * q, col = e % KC, row = e / KC;
         const bool cok = c0 + col < dim;
-        T yv = (T)0, xv = (T)0;
-        if (cok && row < ycnt) yv = gy[(size_t)(FILT ? yid[row] : (uint32_t)(y0 + row)) * dim + c0 + col];
-        if (cok && x0 + row < xcnt) xv = gx[(size_t)(FILT ? xid[row] : (uint32_t)(x0 + row)) * dim + c0 + col];
-        ys[col * PITCH + row] = yv;
-        xs[col * PITCH + row] = xv;
+        py[q] = (T)0; px[q] = (T)0;
+        if (cok && row < ycnt) py[q] = gy[(size_t)(FILT ? yid[row] : (uint32_t)(y0 + row)) * dim + c0 + col];
+        if (cok && x0 + row < xcnt) px[q] = gx[(size_t)(FILT ? xid[row] : (uint32_t)(x0 + row)) * dim + c0 + col];
+      }
+    };
+    fetch(0);
+    for (int c0 = 0; c0 < dim; c0 += KC) {
+#pragma unroll
+      for (int q = 0; q < (TB * KC) / NT; ++q) {
+        const int e = tid + NT * q, col = e % KC, row = e / KC;
+        ys[col * PITCH + row] = py[q];
+        xs[col * PITCH + row] = px[q];
       }
       __syncthreads();
+      if (c0 + KC < dim) fetch(c0 + KC);
       const int kc = min(KC, dim - c0);
+      // (reading column c + 1's operands while column c is summed was measured: no gain -- the loop is
+      // bound by FADD issue, ncu: fma pipe 51 % of peak at 2 FADD per pair-column, not by LDS latency)
 #pragma unroll 4
       for (int c = 0; c < kc; ++c) {
         T ya[8], xb[8];
@@ -331,15 +343,33 @@ cudaError_t launch_lp_p(const LpParams& P, dim3 grid, size_t smem, cudaStream_t 
 
 }  // namespace
 
-int lp_splits(int xrows, int yrows, int sms) {
-  const int nyt = (yrows + TB - 1) / TB, nxt = (xrows + TB - 1) / TB;
-  int s = (2 * sms + nyt - 1) / nyt;
-  if (s > nxt) s = nxt;
-  return s < 1 ? 1 : s;
+// Train-side splits: CTAs are (query tile, split) pairs and a CTA runs its train tiles in sequence, so
+// time ~ waves of CTAs x train tiles per CTA (+ a fixed cost per CTA: query staging, bound bootstrap,
+// publishing).  Pick the split count that minimises it -- 157 query tiles on 148 SMs are 2 waves
+// unsplit, 3 waves at 2 splits, but 17 full waves at 16 -- under a cap on the partial-list scratch.
+static int pick_splits(int ny_tiles, int nxt, int sms, size_t rows_times_k) {
+  if (ny_tiles < 1 || nxt < 1) return 1;
+  int smax = nxt < 64 ? nxt : 64;
+  const size_t cap = ((size_t)1 << 27) / (rows_times_k ? rows_times_k : 1);   // <= 1 GiB of 8-byte keys
+  if ((size_t)smax > cap) smax = cap < 1 ? 1 : (int)cap;
+  int best = 1;
+  double best_cost = 1e300;
+  for (int s = 1; s <= smax; ++s) {
+    const long long ctas = (long long)ny_tiles * s;
+    const long long waves = (ctas + sms - 1) / sms;
+    const int per = (nxt + s - 1) / s;
+    const double cost = (double)waves * (per + 0.5);
+    if (cost < best_cost * 0.98) { best_cost = cost; best = s; }
+  }
+  return best;
+}
+
+int lp_splits(int xrows, int yrows, int k, int sms) {
+  return pick_splits((yrows + TB - 1) / TB, (xrows + TB - 1) / TB, sms, (size_t)(yrows > 0 ? yrows : 0) * k);
 }
 
 size_t lp_partial_bytes(int xrows, int yrows, int k, int sms) {
-  return (size_t)lp_splits(xrows, yrows, sms) * (size_t)yrows * k * sizeof(unsigned long long);
+  return (size_t)lp_splits(xrows, yrows, k, sms) * (size_t)yrows * k * sizeof(unsigned long long);
 }
 
 cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
@@ -357,7 +387,7 @@ cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int 
   LpParams P;
   P.x = dx; P.y = dy; P.xrows = xrows; P.yrows = yrows; P.dim = dim; P.k = k; P.p = p;
   P.nxt = (xrows + TB - 1) / TB;
-  P.splits = lp_splits(xrows, yrows, sms);
+  P.splits = lp_splits(xrows, yrows, k, sms);
   P.partial = partial;
   P.ysel = P.xsel = nullptr; P.tiles = nullptr; P.nysel = 0;
   const dim3 grid((yrows + TB - 1) / TB, P.splits);
@@ -373,16 +403,12 @@ cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int 
 // ---- the filter overload, batched over groups (see the header)
 int lp_filtered_tile_rows() { return TB; }
 
-int lp_filtered_splits(int ntiles, int max_xcnt, int sms) {
-  if (ntiles < 1) return 1;
-  const int nxt = (max_xcnt + TB - 1) / TB;
-  int s = (2 * sms + ntiles - 1) / ntiles;
-  if (s > nxt) s = nxt;
-  return s < 1 ? 1 : s;
+int lp_filtered_splits(int ntiles, int max_xcnt, int nysel, int k, int sms) {
+  return pick_splits(ntiles, (max_xcnt + TB - 1) / TB, sms, (size_t)(nysel > 0 ? nysel : 0) * k);
 }
 
 size_t lp_filtered_partial_bytes(int ntiles, int max_xcnt, int nysel, int k, int sms) {
-  return (size_t)lp_filtered_splits(ntiles, max_xcnt, sms) * (size_t)nysel * k * sizeof(unsigned long long);
+  return (size_t)lp_filtered_splits(ntiles, max_xcnt, nysel, k, sms) * (size_t)nysel * k * sizeof(unsigned long long);
 }
 
 cudaError_t lp_topk_filtered(const float* dx, const float* dy, int dim, int k, double p, const int4* dtiles, int ntiles,
@@ -396,7 +422,7 @@ cudaError_t lp_topk_filtered(const float* dx, const float* dy, int dim, int k, d
   if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
   LpParams P;
   P.x = dx; P.y = dy; P.xrows = 0; P.yrows = 0; P.dim = dim; P.k = k; P.p = p; P.nxt = 0;
-  P.splits = lp_filtered_splits(ntiles, max_xcnt, sms);
+  P.splits = lp_filtered_splits(ntiles, max_xcnt, nysel, k, sms);
   P.partial = partial;
   P.ysel = dysel; P.xsel = dxsel; P.tiles = dtiles; P.nysel = nysel;
   const dim3 grid(ntiles, P.splits);
