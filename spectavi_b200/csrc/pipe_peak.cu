@@ -39,6 +39,9 @@ enum Variant {
   V_SAD4_ACC_IMAD11,   // 1 IMAD per 1 SAD4
   V_SAD4_TILE,         // 8x4 register tile, operands from shared memory (LDS.128)
   V_SAD_SCALAR,        // VABSDIFF.U32 (scalar sad)
+  V_FADD,              // FADD acc, acc, a
+  V_FSUB_ABSADD,       // FADD d, a, -b ; FADD acc, acc, |d|   (K1f's p = 1 pair-column, lp_topk.cu)
+  V_FSUB_FMUL_FADD,    // FADD d ; FMUL d*d ; FADD acc         (K1f's p = 2 pair-column, no FMA contraction)
   V_COUNT
 };
 
@@ -138,6 +141,24 @@ __global__ void __launch_bounds__(256, 2) peak_kernel(const uint32_t* __restrict
     } else if (V == V_SAD_SCALAR) {
 #pragma unroll
       for (int i = 0; i < NACC; ++i) acc[i] = __usad(a[i & 7], b[(i >> 3) & 7], acc[i]);
+    } else if (V == V_FADD) {
+#pragma unroll
+      for (int i = 0; i < NACC; ++i) asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(*reinterpret_cast<float*>(&acc[i])) : "f"(__uint_as_float(a[i & 7])));
+    } else if (V == V_FSUB_ABSADD) {
+#pragma unroll
+      for (int i = 0; i < NACC; ++i) {
+        float d;
+        asm volatile("sub.rn.f32 %0, %1, %2;" : "=f"(d) : "f"(__uint_as_float(a[i & 7])), "f"(__uint_as_float(b[(i >> 3) & 7])));
+        asm volatile("{ .reg .f32 t; abs.f32 t, %1; add.rn.f32 %0, %0, t; }" : "+f"(*reinterpret_cast<float*>(&acc[i])) : "f"(d));
+      }
+    } else if (V == V_FSUB_FMUL_FADD) {
+#pragma unroll
+      for (int i = 0; i < NACC; ++i) {
+        float d;
+        asm volatile("sub.rn.f32 %0, %1, %2;" : "=f"(d) : "f"(__uint_as_float(a[i & 7])), "f"(__uint_as_float(b[(i >> 3) & 7])));
+        asm volatile("mul.rn.f32 %0, %0, %0;" : "+f"(d));
+        asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(*reinterpret_cast<float*>(&acc[i])) : "f"(d));
+      }
     }
   }
   long long t1 = clock64();
@@ -161,6 +182,9 @@ const Desc kDesc[V_COUNT] = {
   {"sad4_acc + 1/4 IMAD", NACC, 4}, {"sad4_acc + 1/1 IMAD", NACC, 4},
   {"sad4 8x4 tile, LDS.128 operands", 128, 4},
   {"VABSDIFF.U32 scalar sad", NACC, 1},
+  {"FADD", NACC, 0},
+  {"f32 sub + |.|add (2 FADD)", NACC, 1},          // op = one pair-column of K1f at p = 1
+  {"f32 sub + mul + add (FADD FMUL FADD)", NACC, 1},
 };
 
 template <int V>
@@ -212,6 +236,7 @@ extern "C" int spv_pipe_peak(int device, int iters, double* out, const char** na
 #define RUN(V) if (!rc) rc = run_variant<V>(sms, cps, iters, din, dout, dcyc, &out[V * 2], &out[V * 2 + 1]);
   RUN(V_SAD4_ACC) RUN(V_SAD4_DP4A) RUN(V_HALF2_ABS) RUN(V_IADD3) RUN(V_LOP3) RUN(V_IMAD) RUN(V_FFMA)
   RUN(V_VIMNMX) RUN(V_VIMNMX3) RUN(V_DP4A) RUN(V_SAD4_ACC_IMAD) RUN(V_SAD4_ACC_IMAD11) RUN(V_SAD4_TILE) RUN(V_SAD_SCALAR)
+  RUN(V_FADD) RUN(V_FSUB_ABSADD) RUN(V_FSUB_FMUL_FADD)
 #undef RUN
   for (int v = 0; v < V_COUNT; ++v) { if (names) names[v] = kDesc[v].name; if (lanes_per_op) lanes_per_op[v] = kDesc[v].lanes_per_op; }
   cudaFree(din); cudaFree(dout); cudaFree(dcyc);

@@ -26,6 +26,15 @@ def run(rows=20000, reps=5):
             ts.append(time.perf_counter() - t0)
         ms = float(np.median(ts) * 1e3)
         out["p=%g" % p] = {"e2e_ms": ms, "Gpairs_per_s": rows * rows / ms / 1e6}
+    # the FP32 issue ceilings K1f's inner loop is built from, measured now (pipe_peak.cu)
+    import ctypes as ct
+    from spectavi_b200._libspectavi import clib
+    o = (ct.c_double * 64)(); names = (ct.c_char_p * 32)(); lanes = (ct.c_double * 32)()
+    clib.spv_pipe_peak.restype = ct.c_int
+    clib.spv_pipe_peak.argtypes = [ct.c_int, ct.c_int, ct.c_void_p, ct.c_void_p, ct.c_void_p]
+    n = clib.spv_pipe_peak(0, 4000, o, names, lanes)
+    out["pipe_peak"] = {names[v].decode(): {"ops_per_clk_sm": o[2 * v], "gops": o[2 * v + 1]} for v in range(n)
+                        if names[v].decode().startswith(("FADD", "f32", "FFMA"))}
     return out
 
 
