@@ -273,6 +273,11 @@ def side_measurements(device):
         out["c5_cascade"] = bench_cascade.run(1_000_000, 128, 3, 1000)
     except Exception as ex:
         out["c5_cascade"] = {"error": repr(ex)[:200]}
+    try:   # KMedians::find_nearest_neighbours at the castle pair's size
+        import bench_kmedians
+        out["kmedians_nn"] = bench_kmedians.run(10000, 132, 5)
+    except Exception as ex:
+        out["kmedians_nn"] = {"error": repr(ex)[:200]}
     return out
 
 
