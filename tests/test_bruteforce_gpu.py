@@ -92,3 +92,21 @@ def test_bruteforce_ties_lexicographic(po, feature):
     gi, gd = feature.nn_bruteforce(x, y, p=1., mu=0., k=4)
     ni, nd = po.numpy_topk(x, y, 4, 1)
     assert (gi == ni).all() and (gd == nd.astype("float32")).all()
+
+
+@pytest.mark.parametrize("k", [1, 2, 16, 17, 40])
+@pytest.mark.parametrize("use_int", [False, True])
+def test_bruteforce_tie_stress_many_tiles(po, feature, k, use_int):
+    """Equal distances everywhere (3-symbol rows), train rows over many tiles and splits, k on both sides of the
+    first-tile bound's limit (16): the result is the lexicographic (dist, idx) top-k whatever order candidates
+    reach the row's list in."""
+    rng = np.random.RandomState(k + 100 * use_int)
+    x = rng.randint(0, 3, (3000, 12)).astype("float32")
+    y = rng.randint(0, 3, (300, 12)).astype("float32")
+    if use_int:
+        x, y = x / 100., y / 100.          # the wrapper rounds 100 * v to int32 (feature.py:286-287)
+    gi, gd = feature.nn_bruteforce(x, y, p=1., mu=0., k=k, use_int=use_int)
+    gi, gd = gi.reshape(300, k), gd.reshape(300, k)
+    xs, ys = (np.round(100 * x), np.round(100 * y)) if use_int else (x, y)
+    ni, nd = po.numpy_topk(xs, ys, k, 1)
+    assert (gi == ni).all() and (gd == nd.astype(gd.dtype)).all()

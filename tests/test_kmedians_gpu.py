@@ -101,3 +101,17 @@ def test_filter_overload_rejects_bad_ids(feature):
         feature.nn_bruteforce_filtered(x, x, [10], [0])
     with pytest.raises(ValueError):
         feature.kmedians_find_nearest_neighbours(x, x, x[:2], np.full(10, 2), x[:2], np.zeros(10), c=1)
+
+
+def test_filter_overload_tie_stress(po, feature):
+    """Equal distances everywhere: with the filters in ascending order the oracle's visiting order is ascending row
+    id, so its result is the lexicographic (dist, idx) top-k -- what the GPU returns for any list order."""
+    rng = np.random.RandomState(8)
+    x = rng.randint(0, 3, (2500, 10)).astype("float32")
+    y = rng.randint(0, 3, (400, 10)).astype("float32")
+    fx = np.sort(rng.choice(2500, 1900, replace=False))
+    fy = np.sort(rng.choice(400, 333, replace=False))
+    for k in (1, 3, 16, 20):
+        oi, od = po.bruteforce_filtered(x, y, fx, fy, k, 1., 0.)
+        gi, gd = feature.nn_bruteforce_filtered(x, y, fx[::-1].copy(), fy[::-1].copy(), p=1., mu=0., k=k)
+        assert (gi == oi).all() and _eq(gd, od)
