@@ -68,6 +68,13 @@ struct LpParams {
   int nysel;                       // entries in ysel (row stride of partial)
 };
 
+// Train rows of a thread's 8 x 8 register tile: columns j = 0..3 are tile rows 4 tx + j, columns 4..7 are
+// 64 + 4 tx + (j - 4), so that the lanes of a quarter-warp read one contiguous 128 B span per LDS.128.
+// (With 8 consecutive rows per thread the 32 B lane stride makes each operand load a 2-way bank conflict.
+// Removing it left the kernel time unchanged, 4.96 ms at 20 k x 20 k x 132: the loop is bound by the FP32
+// pipe -- ncu: math-pipe throttle and dispatch stalls with ~1.9 eligible warps per scheduler -- not by LDS.)
+__device__ __forceinline__ int xrow(int tx, int j) { return (j & 4) * 16 + tx * 4 + (j & 3); }
+
 // key = order-preserving 32 bits of the distance << 32 | train index
 __device__ __forceinline__ uint32_t dist_bits(float d) { return __float_as_uint(d); }   // d >= 0
 __device__ __forceinline__ uint32_t dist_bits(int d) { return (uint32_t)d; }            // d >= 0
@@ -154,9 +161,9 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
       for (int c = 0; c < kc; ++c) {
         T ya[8], xb[8];
         const float4* yp = reinterpret_cast<const float4*>(ys + c * PITCH + ty * 8);
-        const float4* xp = reinterpret_cast<const float4*>(xs + c * PITCH + tx * 8);
+        const float4* xp = reinterpret_cast<const float4*>(xs + c * PITCH + tx * 4);
         *reinterpret_cast<float4*>(&ya[0]) = yp[0]; *reinterpret_cast<float4*>(&ya[4]) = yp[1];
-        *reinterpret_cast<float4*>(&xb[0]) = xp[0]; *reinterpret_cast<float4*>(&xb[4]) = xp[1];
+        *reinterpret_cast<float4*>(&xb[0]) = xp[0]; *reinterpret_cast<float4*>(&xb[4]) = xp[TB / 8];   // + 64 rows
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
@@ -188,7 +195,7 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
         uint32_t mn = THR_NONE;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          if (x0 + tx * 8 + j < xcnt) mn = min(mn, dist_bits(acc[i][j]));
+          if (x0 + xrow(tx, j) < xcnt) mn = min(mn, dist_bits(acc[i][j]));
         int rank = 0;
 #pragma unroll
         for (int o = 0; o < 16; ++o) {
@@ -205,7 +212,7 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
     for (int i = 0; i < 8; ++i) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const bool c = (x0 + tx * 8 + j < xcnt) && dist_bits(acc[i][j]) <= thb[i];   // THR_NONE admits all
+        const bool c = (x0 + xrow(tx, j) < xcnt) && dist_bits(acc[i][j]) <= thb[i];   // THR_NONE admits all
         pend |= (unsigned long long)c << (i * 8 + j);
       }
     }
@@ -230,7 +237,7 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
             if ((pend >> (i * 8 + j)) & 1) {
               if (slot < QCAP) {
                 qkey[slot] = ((unsigned long long)dist_bits(acc[i][j]) << 32) |
-                             (FILT ? xid[tx * 8 + j] : (uint32_t)(x0 + tx * 8 + j));
+                             (FILT ? xid[xrow(tx, j)] : (uint32_t)(x0 + xrow(tx, j)));
                 qrow[slot] = (unsigned short)(ty * 8 + i);
                 pend &= ~(1ull << (i * 8 + j));
               }
