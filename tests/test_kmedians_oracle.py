@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 from conftest import golden
+from oracle import pyoracle
 
 FILTER_CASES = (("k3p1", 3, 1., "fx", "fy"), ("k1p2", 1, 2., "fx", "fy"), ("k3p05", 3, .5, "fx2", "fy"),
                 ("allx", 2, 1., "none", "fy"), ("ally", 2, 1., "fx", "none"))
@@ -67,7 +68,7 @@ def test_oracle_kmedians_empty_cluster_means_all_rows(po):
     assert (oi[rows0] == wi[rows0]).all()
 
 
-needs_ref = pytest.mark.skipif(not __import__("oracle.pyoracle", fromlist=["x"]).have_ref(), reason="oracle/_ref not built here")
+needs_ref = pytest.mark.skipif(not pyoracle.have_ref(), reason="oracle/_ref not built here")
 
 
 @needs_ref
