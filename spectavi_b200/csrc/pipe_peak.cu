@@ -148,14 +148,15 @@ __global__ void __launch_bounds__(256, 2) peak_kernel(const uint32_t* __restrict
 #pragma unroll
       for (int i = 0; i < NACC; ++i) {
         float d;
-        asm volatile("sub.rn.f32 %0, %1, %2;" : "=f"(d) : "f"(__uint_as_float(a[i & 7])), "f"(__uint_as_float(b[(i >> 3) & 7])));
+        // the subtrahend is another chain's accumulator so that the subtraction cannot be hoisted out of the loop
+        asm volatile("sub.rn.f32 %0, %1, %2;" : "=f"(d) : "f"(__uint_as_float(a[i & 7])), "f"(__uint_as_float(acc[(i + 16) & (NACC - 1)])));
         asm volatile("{ .reg .f32 t; abs.f32 t, %1; add.rn.f32 %0, %0, t; }" : "+f"(*reinterpret_cast<float*>(&acc[i])) : "f"(d));
       }
     } else if (V == V_FSUB_FMUL_FADD) {
 #pragma unroll
       for (int i = 0; i < NACC; ++i) {
         float d;
-        asm volatile("sub.rn.f32 %0, %1, %2;" : "=f"(d) : "f"(__uint_as_float(a[i & 7])), "f"(__uint_as_float(b[(i >> 3) & 7])));
+        asm volatile("sub.rn.f32 %0, %1, %2;" : "=f"(d) : "f"(__uint_as_float(a[i & 7])), "f"(__uint_as_float(acc[(i + 16) & (NACC - 1)])));
         asm volatile("mul.rn.f32 %0, %0, %0;" : "+f"(d));
         asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(*reinterpret_cast<float*>(&acc[i])) : "f"(d));
       }
