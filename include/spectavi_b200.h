@@ -152,6 +152,13 @@ int spv_normalize_new_dim(int dim);
 int spv_normalize_device(const float *dx, int rows, int dim, float *dout_f32, uint8_t *dout_u8, void *dws,
                          size_t ws_bytes, void *stream);
 
+/* K1f on device rows: sum |x - y|^p top-k (BruteForceNn.h:37-120), float32 (is_int = 0) or int32 rows.
+ * didx: yrows x k uint64, ddist: yrows x k float32 / int32, ascending, right-aligned and zero-filled in front
+ * when xrows < k (what nn_bruteforce returns into numpy zeros).  dws: spv_nn_bruteforce_ws_bytes() of scratch. */
+size_t spv_nn_bruteforce_ws_bytes(int xrows, int yrows, int k);
+int spv_nn_bruteforce_device(const void *dx, const void *dy, int is_int, int xrows, int yrows, int dim, int k,
+                             double p, uint64_t *didx, void *ddist, void *dws, size_t ws_bytes, void *stream);
+
 /* K0: (uint8)((int)v + 128), the cast of CascadingHashNn.h:236-239 (count % 4 == 0) */
 int spv_f32_to_u8_device(const float *din, uint8_t *dout, size_t count, void *stream);
 /* scratch bytes spv_cascade_device needs (0 = unsupported parameters) */

@@ -115,6 +115,28 @@ int spv_normalize_device(const float* dx, int rows, int dim, float* dout_f32, ui
   return 0;
 }
 
+static int sm_count() {
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+  return sms;
+}
+
+size_t spv_nn_bruteforce_ws_bytes(int xrows, int yrows, int k) {
+  const int sms = sm_count();
+  if (sms <= 0 || xrows < 0 || yrows < 0 || k < 1 || k > LP_MAX_K) return 0;
+  return lp_partial_bytes(xrows, yrows, k, sms) + 8;
+}
+
+int spv_nn_bruteforce_device(const void* dx, const void* dy, int is_int, int xrows, int yrows, int dim, int k, double p,
+                             uint64_t* didx, void* ddist, void* dws, size_t ws_bytes, void* stream) {
+  if (xrows < 0 || yrows < 0 || dim <= 0) return fail("bad shape %d x %d x %d", xrows, yrows, dim);
+  if (k < 1 || k > LP_MAX_K) return fail("k = %d outside [1, %d]", k, LP_MAX_K);
+  if (ws_bytes < spv_nn_bruteforce_ws_bytes(xrows, yrows, k)) return fail("workspace too small");
+  CU_OR_FAIL(lp_topk(dx, dy, is_int != 0, xrows, yrows, dim, k, p, reinterpret_cast<unsigned long long*>(dws), didx, ddist,
+                     (cudaStream_t)stream));
+  return 0;
+}
+
 int spv_f32_to_u8_device(const float* din, uint8_t* dout, size_t count, void* stream) {
   CU_OR_FAIL(f32_to_u8(din, dout, count, (cudaStream_t)stream));
   return 0;

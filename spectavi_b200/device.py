@@ -128,6 +128,32 @@ def normalize_rows(x, want_f32=True, want_u8=True):
     return of, ou
 
 
+clib.spv_nn_bruteforce_ws_bytes.restype = ct.c_size_t
+clib.spv_nn_bruteforce_ws_bytes.argtypes = [ct.c_int, ct.c_int, ct.c_int]
+clib.spv_nn_bruteforce_device.restype = ct.c_int
+clib.spv_nn_bruteforce_device.argtypes = [_vp, _vp, ct.c_int, ct.c_int, ct.c_int, ct.c_int, ct.c_int, ct.c_double, _vp, _vp,
+                                          _vp, ct.c_size_t, _vp]
+
+
+def nn_bruteforce(x, y, p=.5, k=2):
+    """K1f on CUDA tensors: float32 or int32 rows, sum |x - y|^p top-k (BruteForceNn.h:37-120).
+    Returns (idx int64 [yrows, k] holding the uint64 bits, dist float32 / int32 [yrows, k])."""
+    assert x.is_cuda and y.is_cuda and x.dtype == y.dtype and x.dtype in (torch.float32, torch.int32)
+    assert x.is_contiguous() and y.is_contiguous() and x.dim() == 2 and y.dim() == 2 and x.shape[1] == y.shape[1]
+    xrows, dim = x.shape
+    yrows = y.shape[0]
+    nbytes = int(clib.spv_nn_bruteforce_ws_bytes(xrows, yrows, k))
+    if nbytes == 0:
+        raise ValueError("unsupported k")
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    idx = torch.empty((yrows, k), dtype=torch.int64, device=x.device)
+    dist = torch.empty((yrows, k), dtype=x.dtype, device=x.device)
+    _check(clib.spv_nn_bruteforce_device(x.data_ptr(), y.data_ptr(), int(x.dtype == torch.int32), xrows, yrows, dim, k,
+                                         float(p), idx.data_ptr(), dist.data_ptr(), ws.data_ptr(), nbytes, _stream()),
+           "spv_nn_bruteforce_device")
+    return idx, dist
+
+
 def nn_bruteforcel1k2_sharded(x_shard, y, xoffset, group=None):
     """Brute-force L1 k=2 with the train set sharded over the ranks of ``group``
     (SURVEY.md 8e): every rank folds its shard, the key buffers are

@@ -110,3 +110,23 @@ def test_bruteforce_tie_stress_many_tiles(po, feature, k, use_int):
     xs, ys = (np.round(100 * x), np.round(100 * y)) if use_int else (x, y)
     ni, nd = po.numpy_topk(xs, ys, k, 1)
     assert (gi == ni).all() and (gd == nd.astype(gd.dtype)).all()
+
+
+@pytest.mark.parametrize("p,k,use_int", [(1., 2, False), (2., 5, False), (.5, 1, False), (2., 3, True)])
+def test_bruteforce_device_resident(po, p, k, use_int):
+    """Part 2 of the header: the same kernel on device pointers (torch owns the memory and the stream)."""
+    import torch
+    from spectavi_b200 import device as dev
+    rng = np.random.RandomState(int(p * 10) + k)
+    x = rng.randn(1500, 36).astype("float32")
+    y = rng.randn(700, 36).astype("float32")
+    if use_int:
+        x, y = np.round(100 * x).astype("int32"), np.round(100 * y).astype("int32")
+    gi, gd = dev.nn_bruteforce(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), p=p, k=k)
+    oi, od = po.bruteforce(x, y, k, p, 0., use_int=use_int)
+    assert (gi.cpu().numpy().view(np.uint64) == oi).all()
+    assert (gd.cpu().numpy().view(np.uint32) == od.view(np.uint32)).all()
+    # fewer train rows than k: right-aligned, zero-filled in front
+    gi, gd = dev.nn_bruteforce(torch.from_numpy(x[:2]).cuda(), torch.from_numpy(y).cuda(), p=p, k=4)
+    oi, od = po.bruteforce(x[:2], y, 4, p, 0., use_int=use_int)
+    assert (gi.cpu().numpy().view(np.uint64) == oi).all() and (gd.cpu().numpy().view(np.uint32) == od.view(np.uint32)).all()
