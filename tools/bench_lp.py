@@ -26,6 +26,23 @@ def run(rows=20000, reps=5):
             ts.append(time.perf_counter() - t0)
         ms = float(np.median(ts) * 1e3)
         out["p=%g" % p] = {"e2e_ms": ms, "Gpairs_per_s": rows * rows / ms / 1e6}
+    # device-resident: K1f alone, CUDA events on the launching stream, inputs already in HBM
+    import torch
+    from spectavi_b200 import device as dev
+    dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    for p in (1., 2.):
+        for _ in range(3):
+            dev.nn_bruteforce(dx, dy, p=p, k=2)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            dev.nn_bruteforce(dx, dy, p=p, k=2)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        out["p=%g" % p]["device_ms"] = ms
+        out["p=%g" % p]["T_pair_columns_per_s"] = rows * rows * 132 / ms / 1e9
     # the FP32 issue ceilings K1f's inner loop is built from, measured now (pipe_peak.cu)
     import ctypes as ct
     from spectavi_b200._libspectavi import clib
@@ -35,6 +52,12 @@ def run(rows=20000, reps=5):
     n = clib.spv_pipe_peak(0, 4000, o, names, lanes)
     out["pipe_peak"] = {names[v].decode(): {"ops_per_clk_sm": o[2 * v], "gops": o[2 * v + 1]} for v in range(n)
                         if names[v].decode().startswith(("FADD", "f32", "FFMA"))}
+    pk = out["pipe_peak"]
+    out["roofline"] = {"bound": "fp32 pipe", "unit": "T pair-columns/s",
+                       "p=1": {"achieved": out["p=1"]["T_pair_columns_per_s"], "peak": pk["f32 sub + |.|add (2 FADD)"]["gops"] / 1e3},
+                       "p=2": {"achieved": out["p=2"]["T_pair_columns_per_s"], "peak": pk["f32 sub + mul + add (FADD FMUL FADD)"]["gops"] / 1e3}}
+    for q in ("p=1", "p=2"):
+        out["roofline"][q]["frac"] = out["roofline"][q]["achieved"] / out["roofline"][q]["peak"]
     return out
 
 
