@@ -157,6 +157,10 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
       const int kc = min(KC, dim - c0);
       // (reading column c + 1's operands while column c is summed was measured: no gain -- the loop is
       // bound by FADD issue, ncu: fma pipe 51 % of peak at 2 FADD per pair-column, not by LDS latency)
+      // a warp owns 16 query rows; warps whose rows all lie beyond the tile's last query row (ragged last tile,
+      // small clusters of the filter overload: 45 of 128 rows) skip the arithmetic, not the staging or barriers
+      // (filter overload only: in the dense kernel the extra predicate cost 6 % -- measured -- for one ragged tile)
+      if (!FILT || (tid >> 5) * 16 < ycnt)
 #pragma unroll 4
       for (int c = 0; c < kc; ++c) {
         T ya[8], xb[8];
@@ -212,7 +216,7 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
     for (int i = 0; i < 8; ++i) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const bool c = (x0 + xrow(tx, j) < xcnt) && dist_bits(acc[i][j]) <= thb[i];   // THR_NONE admits all
+        const bool c = (!FILT || ty * 8 + i < ycnt) && (x0 + xrow(tx, j) < xcnt) && dist_bits(acc[i][j]) <= thb[i];   // THR_NONE admits all
         pend |= (unsigned long long)c << (i * 8 + j);
       }
     }
