@@ -359,7 +359,9 @@ def run_b200(args):
         h2d = (xn + yr) * dim
         d2h = yr * 2 * (8 + 4)
         if world == 1:
-            nx, ny = hx.numpy(), hy.numpy()
+            # ordinary pageable numpy arrays, as a user's are (NOT views of the pinned tensors above)
+            nx, ny = np.empty(hx.shape, np.uint8), np.empty(hy.shape, np.uint8)
+            nx[...] = hx.numpy(); ny[...] = hy.numpy()
             for _ in range(2):
                 feature.nn_bruteforcel1k2(nx, ny)
             torch.cuda.synchronize()

@@ -123,14 +123,14 @@ static int sm_count() {
 
 size_t spv_nn_bruteforce_ws_bytes(int xrows, int yrows, int k) {
   const int sms = sm_count();
-  if (sms <= 0 || xrows < 0 || yrows < 0 || k < 1 || k > LP_MAX_K) return 0;
+  if (sms <= 0 || xrows < 0 || yrows < 0 || k < 1) return 0;
   return lp_partial_bytes(xrows, yrows, k, sms) + 8;
 }
 
 int spv_nn_bruteforce_device(const void* dx, const void* dy, int is_int, int xrows, int yrows, int dim, int k, double p,
                              uint64_t* didx, void* ddist, void* dws, size_t ws_bytes, void* stream) {
   if (xrows < 0 || yrows < 0 || dim <= 0) return fail("bad shape %d x %d x %d", xrows, yrows, dim);
-  if (k < 1 || k > LP_MAX_K) return fail("k = %d outside [1, %d]", k, LP_MAX_K);
+  if (k < 1) return fail("k = %d must be >= 1", k);
   if (ws_bytes < spv_nn_bruteforce_ws_bytes(xrows, yrows, k)) return fail("workspace too small");
   CU_OR_FAIL(lp_topk(dx, dy, is_int != 0, xrows, yrows, dim, k, p, reinterpret_cast<unsigned long long*>(dws), didx, ddist,
                      (cudaStream_t)stream));
@@ -229,7 +229,7 @@ void spv_normalize_to_ubyte(const float* x, int rows, int dim, NdArray* out) {
 static void lp_entry(const char* fn, const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k,
                      float p, NdArray* outidx, NdArray* outdist) {
   if (xrows < 0 || yrows < 0 || dim <= 0) die(fn, "bad shape %d x %d x %d", xrows, yrows, dim);
-  if (k < 1 || k > LP_MAX_K) die(fn, "k = %d outside [1, %d]", k, LP_MAX_K);
+  if (k < 1) die(fn, "k = %d must be >= 1", k);
   out_alloc(outidx, (uint64_t)yrows, (uint64_t)k);    // Spectavi.cpp:262-265 / :275-278
   out_alloc(outdist, (uint64_t)yrows, (uint64_t)k);
   if (yrows == 0) return;

@@ -642,8 +642,11 @@ __device__ __forceinline__ void top2_merge(unsigned long long& a1, unsigned long
 //      top-2 update per lane and step.
 // The kernel is bound by the latency of dependent random reads (codes -> bucket range -> ids ->
 // rows), so what counts is queries in flight per SM: 4 per warp x 32 warps at 64 registers.
+// NCH = 0: rows wider than 512 bytes -- the chunk count is a run-time value and the query slices are
+// re-read (L1-resident) instead of living in registers.
 template <int NCH>
 __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_kernel(const PrParams P) {
+  constexpr int NYV = NCH > 0 ? NCH : 1;
   constexpr int NQ = PR_WARPS * PR_QPW;                 // queries per CTA
   static_assert(NQ == 16, "the rank computation below takes two slots per lane of an 8-lane group");
   __shared__ __align__(16) int32_t lists[PR_WARPS][PR_QPW][PR_LCAP];
@@ -668,10 +671,11 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
   int32_t* list = lists[warp][q];
 
   // this lane's 16-byte slices of the query row: chunks l8, l8 + 8, ...
-  uint4 yv[NCH];
+  uint4 yv[NYV];
   const uint4* yrow = reinterpret_cast<const uint4*>(P.yu8 + (size_t)r * P.dim);
+  const int nch = NCH > 0 ? NCH : (nk16 + 7) / 8;
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
+  for (int c = 0; c < NYV; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
 
   unsigned long long k1 = KEY_NONE, k2 = KEY_NONE;   // this lane's running top-2 (distinct keys)
   const bool b2 = (l8 & 4) != 0, b1 = (l8 & 2) != 0, b0 = (l8 & 1) != 0;
@@ -694,17 +698,20 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
 #pragma unroll
       for (int u = 0; u < 8; ++u) d[u] = 0;
 #pragma unroll
-      for (int c = 0; c < NCH; ++c) {
+      for (int c = 0; c < nch; ++c) {
+        uint4 yc;
+        if (NCH > 0) yc = yv[NCH > 0 ? c : 0];
+        else yc = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
         uint4 v[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u)
           v[u] = (id[u] >= 0 && l8 + 8 * c < nk16)
                      ? __ldg(reinterpret_cast<const uint4*>(P.xu8 + (size_t)id[u] * P.dim) + l8 + 8 * c)
-                     : yv[c];   // |y - y| = 0
+                     : yc;   // |y - y| = 0
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-          d[u] = sad4(v[u].x, yv[c].x, d[u]); d[u] = sad4(v[u].y, yv[c].y, d[u]);
-          d[u] = sad4(v[u].z, yv[c].z, d[u]); d[u] = sad4(v[u].w, yv[c].w, d[u]);
+          d[u] = sad4(v[u].x, yc.x, d[u]); d[u] = sad4(v[u].y, yc.y, d[u]);
+          d[u] = sad4(v[u].z, yc.z, d[u]); d[u] = sad4(v[u].w, yc.w, d[u]);
         }
       }
       // transposed butterfly over the 8 lanes of the group: lane l8 ends with sum_lanes d[l8]
@@ -829,9 +836,9 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
       const long long row = (long long)blockIdx.x * NQ + mine;
       live = row < P.yrows;
       r = live ? (int)row : P.yrows - 1;
-      const uint4* yr2 = reinterpret_cast<const uint4*>(P.yu8 + (size_t)r * P.dim);
+      yrow = reinterpret_cast<const uint4*>(P.yu8 + (size_t)r * P.dim);
 #pragma unroll
-      for (int c = 0; c < NCH; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yr2 + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
+      for (int c = 0; c < NYV; ++c) yv[c] = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
     }
     while (__any_sync(FULL, done < T)) {
       if (__any_sync(FULL, done < T && listn == PR_LCAP)) drain();   // some group is full: all groups drain
@@ -869,11 +876,20 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
     const unsigned long long o1 = __shfl_xor_sync(FULL, k1, d), o2 = __shfl_xor_sync(FULL, k2, d);
     top2_merge(k1, k2, o1, o2);
   }
-  if (l8 == 0 && live) {   // fold into what other train shards / launches left there
-    unsigned long long e1 = P.keys[r], e2 = P.keys[(size_t)P.yrows + r];
-    top2_merge(e1, e2, k1, k2);
-    P.keys[r] = e1;
-    P.keys[(size_t)P.yrows + r] = e2;
+  if (l8 == 0 && live) {
+    // fold into what other train shards / launches left there: the same two-atomicMin protocol as K1's
+    // fold_key (the loser of the rank-0 exchange is offered to rank 1; a key that is already the best is
+    // not offered again), so folds into one key buffer may run concurrently on any streams
+    const unsigned long long ks[2] = {k1, k2};
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const unsigned long long k = ks[i];
+      if (k == KEY_NONE) continue;
+      const unsigned long long old = atomicMin(P.keys + r, k);
+      if (old == k) continue;
+      const unsigned long long loser = old > k ? old : k;
+      if (loser != KEY_NONE) atomicMin(P.keys + (size_t)P.yrows + r, loser);
+    }
   }
 }
 
@@ -894,7 +910,9 @@ struct Plan {
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 bool make_plan(int xrows, int yrows, int dim, int m, int n, int g, int terms, Plan* pl) {
-  if (dim < 16 || dim % 16 != 0 || dim > 512 || m < 1 || m > 31 || n < 1 || g < 0) return false;
+  if (dim < 16 || dim % 16 != 0 || m < 1 || m > 31 || n < 1 || g < 0 || xrows < 0 || yrows < 0) return false;
+  // bucket counts, scan, cursor and id positions are uint32 / int32 over the concatenated n * xrows axis
+  if ((unsigned long long)n * (unsigned long long)(xrows > 0 ? xrows : 1) >= (1ull << 31)) return false;
   pl->terms = terms;
   pl->nb = g < m ? g : m;                       // :153-159 keeps at most m pairs
   if (pl->nb > 12 || ((long long)n << pl->nb) > (1ll << 24)) return false;
@@ -902,7 +920,7 @@ bool make_plan(int xrows, int yrows, int dim, int m, int n, int g, int terms, Pl
   pl->MP = (m + 7) / 8 * 8;
   const int nkc = dim / 8;
   const size_t a_bytes = (size_t)(HP_KPANEL / 8) * HP_ROWS * 16, budget = 190 * 1024;
-  int nmax = (int)((budget - a_bytes - 64) / ((size_t)terms * nkc * 16)) / 16 * 16;
+  int nmax = (int)((budget - a_bytes - 64) / ((size_t)terms * nkc * 16)) / 16 * 16;   // shrinks with dim: wide rows take fewer tables per pass
   if (nmax > 256) nmax = 256;
   int tpg = nmax / pl->MP;
   if (tpg > n) tpg = n;
@@ -1011,9 +1029,12 @@ void build_image(const Plan& pl, const float* ddict, int n, int dim, int m, __nv
 }  // namespace
 
 size_t cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g) {
-  Plan pl;
-  if (!make_plan(xrows, yrows, dim, m, n, g, 3, &pl)) return 0;
-  return pl.total;
+  // the layout depends on the number of bf16 terms (tables per pass -> padded image size); a caller that
+  // allocates exactly this many bytes must be safe for every dict_terms, so: the largest of the plans
+  Plan p1, p3;
+  const bool ok1 = make_plan(xrows, yrows, dim, m, n, g, 1, &p1), ok3 = make_plan(xrows, yrows, dim, m, n, g, 3, &p3);
+  if (!ok1) return 0;
+  return ok3 && p3.total > p1.total ? p3.total : p1.total;
 }
 
 cudaError_t f32_to_u8(const float* din, uint8_t* dout, size_t count, cudaStream_t stream) {
@@ -1050,6 +1071,7 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
   Plan pl;
   if (dict_terms != 0 && dict_terms != 1 && dict_terms != 3) return cudaErrorInvalidValue;
   if (!plan_for(xrows, yrows, dim, m, n, g, dict_terms, &pl) || ws_bytes < pl.total) return cudaErrorInvalidValue;
+  if ((unsigned long long)xoffset + (unsigned long long)xrows > 0xFFFFFFFFull) return cudaErrorInvalidValue;   // 32 index bits per key
   int dev = 0, sms = 0;
   cudaError_t e;
   if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
@@ -1089,7 +1111,8 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
     case 1: probe_rerank_kernel<1><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
     case 2: probe_rerank_kernel<2><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
     case 3: probe_rerank_kernel<3><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
-    default: probe_rerank_kernel<4><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
+    case 4: probe_rerank_kernel<4><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
+    default: probe_rerank_kernel<0><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
   }
   count_launch();
   return cudaGetLastError();

@@ -10,12 +10,12 @@
 #include <cstdlib>
 #include <random>
 #include <cstring>
+#include <memory>
+#include <thread>
 #include <vector>
 
 namespace spv {
 namespace {
-
-std::mutex g_mu;
 
 struct Buf {
   void* p = nullptr;
@@ -31,9 +31,25 @@ struct Buf {
   }
 };
 
+// One upload lane: a copy stream and two pinned staging buffers.  The caller's arrays are ordinary pageable
+// numpy memory (Spectavi.cpp:284-298 hands over raw pointers), so every byte goes pageable -> pinned (CPU
+// memcpy) -> device (DMA); with two buffers the memcpy of sub-chunk i + 1 runs under the DMA of sub-chunk i,
+// and -- because the DMA sits on its own stream -- under whatever the compute stream is doing.
+constexpr size_t LANE_BYTES = (size_t)4 << 20;
+struct Lane {
+  cudaStream_t copy = nullptr;
+  void* pin[2] = {nullptr, nullptr};
+  cudaEvent_t done[2] = {nullptr, nullptr};   // the DMA out of pin[b] has finished
+  cudaEvent_t ready = nullptr;                // the last piece handed to this lane is on the device
+  bool used[2] = {false, false};
+  int turn = 0;
+};
+
 struct Gpu {
   int dev = -1;
   cudaStream_t stream = nullptr;
+  Lane lane[4];
+  bool lanes_ready = false;
   Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws, rws, sel;
 };
 
@@ -43,13 +59,28 @@ struct Nccl {
   ncclResult_t (*GroupStart)() = nullptr;
   ncclResult_t (*GroupEnd)() = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
-  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
   std::vector<ncclComm_t> comms;
 };
 
-struct Runtime {
+}  // namespace
+
+// A context = the streams, staging lanes and scratch buffers one call works with.  The reference's functions are
+// re-entrant (no globals), so concurrent callers must not serialise on one set of buffers: single-GPU calls take a
+// context from a pool (a new one is made when all are busy); the multi-GPU layout (SPECTAVI_GPUS > 1) has one
+// context, because its NCCL communicators admit one collective sequence at a time.
+struct Ctx {
   std::vector<Gpu> gpus;
+};
+
+namespace {
+
+struct Runtime {
+  std::mutex mu;                                  // guards init, the pool and nothing else
+  std::vector<int> devs;
+  std::vector<std::unique_ptr<Ctx>> pool;         // idle single-GPU contexts
+  std::unique_ptr<Ctx> multi;                     // the multi-GPU context
+  std::mutex multi_mu;                            // held for the whole of a multi-GPU call
   Nccl nccl;
   bool ready = false;
 };
@@ -78,15 +109,26 @@ void load_nccl(const char* fn, int ngpu) {
   n.field = reinterpret_cast<decltype(n.field)>(dlsym(n.lib, name));      \
   if (!n.field) die(fn, "NCCL symbol %s missing", name);
   SYM(CommInitAll, "ncclCommInitAll") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
-  SYM(AllGather, "ncclAllGather") SYM(Broadcast, "ncclBroadcast") SYM(GetErrorString, "ncclGetErrorString")
+  SYM(AllGather, "ncclAllGather") SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
-  std::vector<int> devs(ngpu);
-  for (int g = 0; g < ngpu; ++g) devs[g] = g_rt.gpus[g].dev;
   n.comms.resize(ngpu);
-  NC(fn, n.CommInitAll(n.comms.data(), ngpu, devs.data()));
+  NC(fn, n.CommInitAll(n.comms.data(), ngpu, g_rt.devs.data()));
 }
 
-void init_runtime(const char* fn) {
+std::unique_ptr<Ctx> make_ctx(const char* fn) {
+  std::unique_ptr<Ctx> c(new Ctx);
+  c->gpus.resize(g_rt.devs.size());
+  for (size_t g = 0; g < g_rt.devs.size(); ++g) {
+    Gpu& G = c->gpus[g];
+    G.dev = g_rt.devs[g];
+    CU(fn, cudaSetDevice(G.dev));
+    CU(fn, cudaStreamCreateWithFlags(&G.stream, cudaStreamNonBlocking));
+  }
+  CU(fn, cudaSetDevice(g_rt.devs[0]));
+  return c;
+}
+
+void init_runtime(const char* fn) {   // g_rt.mu held
   if (g_rt.ready) return;
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -99,27 +141,208 @@ void init_runtime(const char* fn) {
   }
   int first = 0;
   cudaGetDevice(&first);   // respect the caller's current device for the 1-GPU case
-  g_rt.gpus.resize(want);
-  for (int g = 0; g < want; ++g) {
-    Gpu& G = g_rt.gpus[g];
-    G.dev = (want == 1) ? first : g;
-    CU(fn, cudaSetDevice(G.dev));
-    CU(fn, cudaStreamCreateWithFlags(&G.stream, cudaStreamNonBlocking));
+  g_rt.devs.resize(want);
+  for (int g = 0; g < want; ++g) g_rt.devs[g] = (want == 1) ? first : g;
+  if (want > 1) {
+    g_rt.multi = make_ctx(fn);
+    load_nccl(fn, want);
+    CU(fn, cudaSetDevice(g_rt.devs[0]));
   }
-  if (want > 1) load_nccl(fn, want);
-  CU(fn, cudaSetDevice(g_rt.gpus[0].dev));
   g_rt.ready = true;
+}
+
+// ---- staged uploads ------------------------------------------------------------------------------------
+void lanes_init(const char* fn, Gpu& D) {
+  if (D.lanes_ready) return;
+  for (Lane& L : D.lane) {
+    CU(fn, cudaStreamCreateWithFlags(&L.copy, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+      CU(fn, cudaHostAlloc(&L.pin[b], LANE_BYTES, cudaHostAllocDefault));
+      CU(fn, cudaEventCreateWithFlags(&L.done[b], cudaEventDisableTiming));
+    }
+    CU(fn, cudaEventCreateWithFlags(&L.ready, cudaEventDisableTiming));
+  }
+  D.lanes_ready = true;
+}
+
+// pageable host -> device through the lane's pinned buffers; returns once the last sub-chunk is QUEUED.
+// The device's current-device must be D's.  `ready` is recorded behind the piece.
+void lane_upload(const char* fn, Lane& L, void* dst, const void* src, size_t bytes) {
+  const char* s = static_cast<const char*>(src);
+  char* d = static_cast<char*>(dst);
+  for (size_t off = 0; off < bytes; off += LANE_BYTES) {
+    const size_t n = bytes - off < LANE_BYTES ? bytes - off : LANE_BYTES;
+    const int b = L.turn;
+    L.turn ^= 1;
+    if (L.used[b]) CU(fn, cudaEventSynchronize(L.done[b]));
+    memcpy(L.pin[b], s + off, n);
+    CU(fn, cudaMemcpyAsync(d + off, L.pin[b], n, cudaMemcpyHostToDevice, L.copy));
+    CU(fn, cudaEventRecord(L.done[b], L.copy));
+    L.used[b] = true;
+  }
+  CU(fn, cudaEventRecord(L.ready, L.copy));
+}
+
+// Piece sizes of a streamed matrix: the first piece is small, so that compute starts after a fraction of a
+// millisecond of upload, and the pieces double up to `cap` rows so that the launch count stays small.
+std::vector<int> piece_rows(int rows, int first, int cap, int align) {
+  std::vector<int> v;
+  int n = first;
+  while (rows > 0) {
+    int take = n < rows ? n : rows;
+    if (rows - take < first / 2) take = rows;          // no sliver at the end
+    else take = take / align * align;
+    v.push_back(take);
+    rows -= take;
+    if (n < cap) n *= 2;
+  }
+  return v;
+}
+
+// K1 over one GPU's train shard, inputs streamed from pageable host memory (the body of HostCall::l1k2 for one
+// device; with SPECTAVI_GPUS > 1 one host thread per device runs it).  Query rows go up first in doubling pieces,
+// each matched against the first, small train piece as soon as it has landed; then the remaining train pieces,
+// each against all query rows.  K1 folds into one key buffer across launches (xoffset) and seeds its thresholds
+// from it (l1_top2.cu), so the chunking costs no extra slow-path work.  Nothing is synchronised here.
+void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* y, int x0, int xn, int yrows, int dim) {
+  CU(fn, cudaSetDevice(D.dev));
+  lanes_init(fn, D);
+  const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
+  CU(fn, D.y.ensure(ybytes));
+  CU(fn, D.keys.ensure(kbytes));
+  CU(fn, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
+  if (xn <= 0) return;
+  CU(fn, D.x.ensure((size_t)xn * dim));
+  Lane& L = D.lane[0];
+  // first train piece sized so that matching it against all query rows takes about as long as uploading them
+  // (x0 * yrows * dim / 4 sad-ops at ~17 T/s  vs  yrows * dim bytes at ~10 GB/s  =>  ~7 k rows, any shape)
+  const std::vector<int> xp = piece_rows(xn, 8192, 65536, 64), yp = piece_rows(yrows, 8192, 131072, 256);
+  uint8_t* dx = (uint8_t*)D.x.p;
+  uint8_t* dy = (uint8_t*)D.y.p;
+  unsigned long long* dk = (unsigned long long*)D.keys.p;
+  lane_upload(fn, L, dx, x + (size_t)x0 * dim, (size_t)xp[0] * dim);
+  int yo = 0;
+  for (int rows : yp) {
+    lane_upload(fn, L, dy + (size_t)yo * dim, y + (size_t)yo * dim, (size_t)rows * dim);
+    CU(fn, cudaStreamWaitEvent(D.stream, L.ready, 0));
+    CU(fn, l1_top2_u8(dx, dy + (size_t)yo * dim, xp[0], rows, dim, (uint32_t)x0, dk + yo, D.stream, yrows));
+    yo += rows;
+  }
+  int xo = xp[0];
+  for (size_t i = 1; i < xp.size(); ++i) {
+    lane_upload(fn, L, dx + (size_t)xo * dim, x + (size_t)(x0 + xo) * dim, (size_t)xp[i] * dim);
+    CU(fn, cudaStreamWaitEvent(D.stream, L.ready, 0));
+    CU(fn, l1_top2_u8(dx + (size_t)xo * dim, dy, xp[i], yrows, dim, (uint32_t)(x0 + xo), dk, D.stream, yrows));
+    xo += xp[i];
+  }
+}
+
+// float32 rows -> device uint8 (value + 128): upload through `nl` lanes in parallel (each lane streams a
+// contiguous slice of the rows with its own host thread, so the pageable -> pinned memcpy -- the slow half of
+// the path at ~10 GB/s per thread -- runs nl-wide), K0 converts each sub-chunk on the lane's stream as it lands
+// (CascadingHashNn.h:236-239), and the compute stream waits for every lane.  dtmp: nl * 2 * LANE_BYTES of scratch.
+void upload_f32_as_u8(const char* fn, Gpu& D, const float* src, size_t count, uint8_t* dst, float* dtmp) {
+  lanes_init(fn, D);
+  const size_t per_chunk = LANE_BYTES / 4;                     // floats per sub-chunk
+  const size_t nchunks = (count + per_chunk - 1) / per_chunk;
+  int nl = (int)(nchunks < 4 ? (nchunks ? nchunks : 1) : 4);
+  auto work = [&](int li) {
+    cudaSetDevice(D.dev);
+    Lane& L = D.lane[li];
+    const size_t c0 = nchunks * li / nl, c1 = nchunks * (li + 1) / nl;
+    for (size_t c = c0; c < c1; ++c) {
+      const size_t off = c * per_chunk, n = count - off < per_chunk ? count - off : per_chunk;
+      const int b = L.turn;
+      L.turn ^= 1;
+      if (L.used[b]) CU(fn, cudaEventSynchronize(L.done[b]));
+      memcpy(L.pin[b], src + off, n * 4);
+      float* dt = dtmp + ((size_t)li * 2 + b) * per_chunk;     // the device-side twin of pin[b]
+      CU(fn, cudaMemcpyAsync(dt, L.pin[b], n * 4, cudaMemcpyHostToDevice, L.copy));
+      CU(fn, f32_to_u8(dt, dst + off, n, L.copy));
+      CU(fn, cudaEventRecord(L.done[b], L.copy));
+      L.used[b] = true;
+    }
+    CU(fn, cudaEventRecord(L.ready, L.copy));
+  };
+  if (nl == 1) work(0);
+  else {
+    std::vector<std::thread> th;
+    for (int li = 1; li < nl; ++li) th.emplace_back(work, li);
+    work(0);
+    for (std::thread& t : th) t.join();
+  }
+  for (int li = 0; li < nl; ++li) CU(fn, cudaStreamWaitEvent(D.stream, D.lane[li].ready, 0));
+}
+
+// run f(g) for every GPU of the context: inline for one, one host thread per GPU otherwise
+template <typename F>
+void per_gpu(Ctx& c, F f) {
+  const int G = (int)c.gpus.size();
+  if (G == 1) { f(0); return; }
+  std::vector<std::thread> th;
+  for (int g = 1; g < G; ++g) th.emplace_back(f, g);
+  f(0);
+  for (std::thread& t : th) t.join();
+}
+
+void sync_all(const char* fn, Ctx& c) {
+  for (Gpu& D : c.gpus) {
+    CU(fn, cudaSetDevice(D.dev));
+    CU(fn, cudaStreamSynchronize(D.stream));
+  }
+}
+
+// all-gather the per-GPU key buffers, K5 merge on GPU 0; no-op for one GPU
+void merge_shards(const char* fn, Ctx& c, int yrows) {
+  const int G = (int)c.gpus.size();
+  if (G == 1) return;
+  const size_t kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
+  for (Gpu& D : c.gpus) {
+    CU(fn, cudaSetDevice(D.dev));
+    CU(fn, D.gather.ensure(kbytes * G));
+  }
+  NC(fn, g_rt.nccl.GroupStart());
+  for (int g = 0; g < G; ++g)
+    NC(fn, g_rt.nccl.AllGather(c.gpus[g].keys.p, c.gpus[g].gather.p, (size_t)2 * yrows, ncclUint64, g_rt.nccl.comms[g],
+                               c.gpus[g].stream));
+  NC(fn, g_rt.nccl.GroupEnd());
+  Gpu& R = c.gpus[0];
+  CU(fn, cudaSetDevice(R.dev));
+  CU(fn, keys_merge((unsigned long long*)R.keys.p, (const unsigned long long*)R.gather.p, G, yrows, R.stream));
 }
 
 }  // namespace
 
-HostCall::HostCall(const char* fn) : fn_(fn), lock_(g_mu) { init_runtime(fn); }
-HostCall::~HostCall() {}
+HostCall::HostCall(const char* fn) : fn_(fn) {
+  cudaGetDevice(&prev_dev_);
+  std::unique_lock<std::mutex> lk(g_rt.mu);
+  init_runtime(fn);
+  if (g_rt.multi) {
+    lk.unlock();
+    multi_lock_ = std::unique_lock<std::mutex>(g_rt.multi_mu);
+    ctx_ = g_rt.multi.get();
+    return;
+  }
+  if (!g_rt.pool.empty()) {
+    ctx_ = g_rt.pool.back().release();
+    g_rt.pool.pop_back();
+  } else {
+    ctx_ = make_ctx(fn).release();
+  }
+}
+
+HostCall::~HostCall() {
+  if (!multi_lock_.owns_lock() && ctx_) {
+    std::lock_guard<std::mutex> lk(g_rt.mu);
+    g_rt.pool.emplace_back(ctx_);
+  }
+  cudaSetDevice(prev_dev_);
+}
 
 // K6 on the merged key buffer of GPU 0: ratio test + compaction on the device, then only
 // count x 16 bytes come back (instead of yrows x 2 x 12)
 void HostCall::deliver_matches(const MatchSink& ms, int yrows, bool dist_f32) {
-  Gpu& R = g_rt.gpus[0];
+  Gpu& R = ctx_->gpus[0];
   CU(fn_, cudaSetDevice(R.dev));
   const size_t wsb = ratio_ws_bytes(yrows);
   CU(fn_, R.rws.ensure(wsb + 16));
@@ -129,10 +352,7 @@ void HostCall::deliver_matches(const MatchSink& ms, int yrows, bool dist_f32) {
                         dcount, R.rws.p, wsb, R.stream));
   unsigned count = 0;
   CU(fn_, cudaMemcpyAsync(&count, dcount, sizeof(count), cudaMemcpyDeviceToHost, R.stream));
-  for (size_t g = 0; g < g_rt.gpus.size(); ++g) {
-    CU(fn_, cudaSetDevice(g_rt.gpus[g].dev));
-    CU(fn_, cudaStreamSynchronize(g_rt.gpus[g].stream));
-  }
+  sync_all(fn_, *ctx_);
   CU(fn_, cudaSetDevice(R.dev));
   uint64_t* out = ms.alloc(count);
   if (count) {
@@ -143,62 +363,22 @@ void HostCall::deliver_matches(const MatchSink& ms, int yrows, bool dist_f32) {
 
 void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist,
                     const MatchSink* ms) {
-  const int G = (int)g_rt.gpus.size();
-  const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
+  Ctx& c = *ctx_;
+  const int G = (int)c.gpus.size();
   const int per = (xrows + G - 1) / G;   // train rows per GPU
-  int prev = 0;
-  cudaGetDevice(&prev);
-  // stage inputs: query rows to GPU 0 (broadcast below), train shard g to GPU g
-  for (int g = 0; g < G; ++g) {
-    Gpu& D = g_rt.gpus[g];
-    CU(fn_, cudaSetDevice(D.dev));
-    const int x0 = g * per < xrows ? g * per : xrows;
+  const char* fn = fn_;
+  // every GPU streams its own train shard and its own copy of the query rows over its own PCIe link
+  per_gpu(c, [&](int g) {
+    const int x0 = (long long)g * per < xrows ? g * per : xrows;
     const int xn = (x0 + per <= xrows) ? per : xrows - x0;
-    CU(fn_, D.y.ensure(ybytes));
-    CU(fn_, D.keys.ensure(kbytes));
-    if (xn > 0) {
-      CU(fn_, D.x.ensure((size_t)xn * dim));
-      CU(fn_, cudaMemcpyAsync(D.x.p, x + (size_t)x0 * dim, (size_t)xn * dim, cudaMemcpyHostToDevice, D.stream));
-    }
-    if (g == 0) CU(fn_, cudaMemcpyAsync(D.y.p, y, ybytes, cudaMemcpyHostToDevice, D.stream));
-    CU(fn_, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
-  }
-  if (G > 1) {
-    NC(fn_, g_rt.nccl.GroupStart());
-    for (int g = 0; g < G; ++g)
-      NC(fn_, g_rt.nccl.Broadcast(g_rt.gpus[0].y.p, g_rt.gpus[g].y.p, ybytes, ncclUint8, 0, g_rt.nccl.comms[g],
-                                  g_rt.gpus[g].stream));
-    NC(fn_, g_rt.nccl.GroupEnd());
-  }
-  // K1 on every shard
-  for (int g = 0; g < G; ++g) {
-    Gpu& D = g_rt.gpus[g];
-    const int x0 = g * per < xrows ? g * per : xrows;
-    const int xn = (x0 + per <= xrows) ? per : xrows - x0;
-    CU(fn_, cudaSetDevice(D.dev));
-    CU(fn_, l1_top2_u8((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, (uint32_t)x0,
-                       (unsigned long long*)D.keys.p, D.stream));
-  }
-  Gpu& R = g_rt.gpus[0];
-  if (G > 1) {
-    // all-gather the per-GPU key buffers, K5 merge on GPU 0
-    for (int g = 0; g < G; ++g) {
-      CU(fn_, cudaSetDevice(g_rt.gpus[g].dev));
-      CU(fn_, g_rt.gpus[g].gather.ensure(kbytes * G));
-    }
-    NC(fn_, g_rt.nccl.GroupStart());
-    for (int g = 0; g < G; ++g)
-      NC(fn_, g_rt.nccl.AllGather(g_rt.gpus[g].keys.p, g_rt.gpus[g].gather.p, (size_t)2 * yrows, ncclUint64,
-                                  g_rt.nccl.comms[g], g_rt.gpus[g].stream));
-    NC(fn_, g_rt.nccl.GroupEnd());
-    CU(fn_, cudaSetDevice(R.dev));
-    CU(fn_, keys_merge((unsigned long long*)R.keys.p, (const unsigned long long*)R.gather.p, G, yrows, R.stream));
-  }
+    l1k2_stream_shard(fn, c.gpus[g], x, y, x0, xn, yrows, dim);
+  });
+  merge_shards(fn_, c, yrows);
   if (ms) {
     deliver_matches(*ms, yrows, false);
-    cudaSetDevice(prev);
     return;
   }
+  Gpu& R = c.gpus[0];
   CU(fn_, cudaSetDevice(R.dev));
   CU(fn_, R.oidx.ensure((size_t)yrows * 2 * sizeof(uint64_t)));
   CU(fn_, R.odist.ensure((size_t)yrows * 2 * sizeof(int32_t)));
@@ -206,11 +386,7 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
                             R.stream));
   CU(fn_, cudaMemcpyAsync(idx, R.oidx.p, (size_t)yrows * 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, R.stream));
   CU(fn_, cudaMemcpyAsync(dist, R.odist.p, (size_t)yrows * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, R.stream));
-  for (int g = 0; g < G; ++g) {
-    CU(fn_, cudaSetDevice(g_rt.gpus[g].dev));
-    CU(fn_, cudaStreamSynchronize(g_rt.gpus[g].stream));
-  }
-  cudaSetDevice(prev);
+  sync_all(fn_, c);
 }
 
 void cascade_dictionary(unsigned seed, int dim, int m, int n, bool quantize, float* out) {
@@ -236,72 +412,44 @@ unsigned cascade_seed() {
 
 void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
                        uint64_t* idx, float* dist, const MatchSink* ms) {
-  const int G = (int)g_rt.gpus.size();
-  const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
+  Ctx& c = *ctx_;
+  const int G = (int)c.gpus.size();
+  const size_t ybytes = (size_t)yrows * dim;
   const int per = (xrows + G - 1) / G;   // train rows per GPU, as for brute force
   std::vector<float> hdict((size_t)n * dim * m);
   cascade_dictionary(cascade_seed(), dim, m, n, true, hdict.data());
-  int prev = 0;
-  cudaGetDevice(&prev);
-  for (int gi = 0; gi < G; ++gi) {
-    Gpu& D = g_rt.gpus[gi];
-    CU(fn_, cudaSetDevice(D.dev));
-    const int x0 = gi * per < xrows ? gi * per : xrows;
+  const char* fn = fn_;
+  // per GPU: its train shard and all query rows go up as float32 through the staging lanes, K0 turns each
+  // sub-chunk into uint8 as it lands, then K2-K4 on the shard with the SAME dictionary
+  per_gpu(c, [&](int gi) {
+    Gpu& D = c.gpus[gi];
+    CU(fn, cudaSetDevice(D.dev));
+    const int x0 = (long long)gi * per < xrows ? gi * per : xrows;
     const int xn = (x0 + per <= xrows) ? per : xrows - x0;
     const size_t wsb = cascade_ws_bytes(xn, yrows, dim, m, n, g);
-    if (wsb == 0) die(fn_, "unsupported parameters dim=%d m=%d n=%d g=%d (need dim %% 16 == 0, dim <= 512, 1 <= m <= 31, g <= 12)", dim, m, n, g);
-    CU(fn_, D.y.ensure(ybytes));
-    CU(fn_, D.keys.ensure(kbytes));
-    CU(fn_, D.dict.ensure(hdict.size() * 4));
-    CU(fn_, D.ws.ensure(wsb));
-    CU(fn_, cudaMemcpyAsync(D.dict.p, hdict.data(), hdict.size() * 4, cudaMemcpyHostToDevice, D.stream));
+    if (wsb == 0) die(fn, "unsupported parameters dim=%d m=%d n=%d g=%d (need dim %% 16 == 0, 1 <= m <= 31, min(g, m) <= 12, n * 2^g <= 2^24, n * rows < 2^31)", dim, m, n, g);
+    CU(fn, D.y.ensure(ybytes));
+    CU(fn, D.keys.ensure((size_t)2 * yrows * sizeof(unsigned long long)));
+    CU(fn, D.dict.ensure(hdict.size() * 4));
+    CU(fn, D.ws.ensure(wsb));
+    CU(fn, D.xf.ensure((size_t)4 * 2 * LANE_BYTES));   // device twins of the pinned staging buffers
+    CU(fn, cudaMemcpyAsync(D.dict.p, hdict.data(), hdict.size() * 4, cudaMemcpyHostToDevice, D.stream));
+    CU(fn, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
     if (xn > 0) {
-      CU(fn_, D.xf.ensure((size_t)xn * dim * 4));
-      CU(fn_, D.x.ensure((size_t)xn * dim));
-      CU(fn_, cudaMemcpyAsync(D.xf.p, x + (size_t)x0 * dim, (size_t)xn * dim * 4, cudaMemcpyHostToDevice, D.stream));
-      CU(fn_, f32_to_u8((const float*)D.xf.p, (uint8_t*)D.x.p, (size_t)xn * dim, D.stream));   // CascadingHashNn.h:236-239
+      CU(fn, D.x.ensure((size_t)xn * dim));
+      upload_f32_as_u8(fn, D, x + (size_t)x0 * dim, (size_t)xn * dim, (uint8_t*)D.x.p, (float*)D.xf.p);   // CascadingHashNn.h:236-239
     }
-    if (gi == 0) {
-      CU(fn_, D.yf.ensure(ybytes * 4));
-      CU(fn_, cudaMemcpyAsync(D.yf.p, y, ybytes * 4, cudaMemcpyHostToDevice, D.stream));
-      CU(fn_, f32_to_u8((const float*)D.yf.p, (uint8_t*)D.y.p, ybytes, D.stream));
-    }
-    CU(fn_, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
-  }
-  if (G > 1) {
-    NC(fn_, g_rt.nccl.GroupStart());
-    for (int gi = 0; gi < G; ++gi)
-      NC(fn_, g_rt.nccl.Broadcast(g_rt.gpus[0].y.p, g_rt.gpus[gi].y.p, ybytes, ncclUint8, 0, g_rt.nccl.comms[gi],
-                                  g_rt.gpus[gi].stream));
-    NC(fn_, g_rt.nccl.GroupEnd());
-  }
-  for (int gi = 0; gi < G; ++gi) {
-    Gpu& D = g_rt.gpus[gi];
-    const int x0 = gi * per < xrows ? gi * per : xrows;
-    const int xn = (x0 + per <= xrows) ? per : xrows - x0;
-    CU(fn_, cudaSetDevice(D.dev));
-    CU(fn_, cascade_match((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, m, n, g, (const float*)D.dict.p, 0,
-                          (uint32_t)x0, (unsigned long long*)D.keys.p, D.ws.p, D.ws.cap, D.stream));
-  }
-  Gpu& R = g_rt.gpus[0];
-  if (G > 1) {
-    for (int gi = 0; gi < G; ++gi) {
-      CU(fn_, cudaSetDevice(g_rt.gpus[gi].dev));
-      CU(fn_, g_rt.gpus[gi].gather.ensure(kbytes * G));
-    }
-    NC(fn_, g_rt.nccl.GroupStart());
-    for (int gi = 0; gi < G; ++gi)
-      NC(fn_, g_rt.nccl.AllGather(g_rt.gpus[gi].keys.p, g_rt.gpus[gi].gather.p, (size_t)2 * yrows, ncclUint64,
-                                  g_rt.nccl.comms[gi], g_rt.gpus[gi].stream));
-    NC(fn_, g_rt.nccl.GroupEnd());
-    CU(fn_, cudaSetDevice(R.dev));
-    CU(fn_, keys_merge((unsigned long long*)R.keys.p, (const unsigned long long*)R.gather.p, G, yrows, R.stream));
-  }
+    upload_f32_as_u8(fn, D, y, ybytes, (uint8_t*)D.y.p, (float*)D.xf.p);
+    CU(fn, cascade_match((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, m, n, g, (const float*)D.dict.p, 0,
+                         (uint32_t)x0, (unsigned long long*)D.keys.p, D.ws.p, D.ws.cap, D.stream));
+  });
+  sync_all(fn_, c);        // hdict is about to go away; the collective below starts from quiescent streams
+  merge_shards(fn_, c, yrows);
   if (ms) {
     deliver_matches(*ms, yrows, true);
-    cudaSetDevice(prev);
     return;
   }
+  Gpu& R = c.gpus[0];
   CU(fn_, cudaSetDevice(R.dev));
   const size_t ib = (size_t)yrows * kcols * sizeof(uint64_t), db = (size_t)yrows * kcols * sizeof(float);
   CU(fn_, R.oidx.ensure(ib));
@@ -311,17 +459,11 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
   CU(fn_, keys_finalize_f32((const unsigned long long*)R.keys.p, yrows, kcols, (uint64_t*)R.oidx.p, (float*)R.odist.p, R.stream));
   CU(fn_, cudaMemcpyAsync(idx, R.oidx.p, ib, cudaMemcpyDeviceToHost, R.stream));
   CU(fn_, cudaMemcpyAsync(dist, R.odist.p, db, cudaMemcpyDeviceToHost, R.stream));
-  for (int gi = 0; gi < G; ++gi) {
-    CU(fn_, cudaSetDevice(g_rt.gpus[gi].dev));
-    CU(fn_, cudaStreamSynchronize(g_rt.gpus[gi].stream));
-  }
-  cudaSetDevice(prev);
+  sync_all(fn_, c);
 }
 
 void HostCall::normalize(const float* x, int rows, int dim, float* out) {
-  Gpu& D = g_rt.gpus[0];
-  int prev = 0;
-  cudaGetDevice(&prev);
+  Gpu& D = ctx_->gpus[0];
   CU(fn_, cudaSetDevice(D.dev));
   const size_t ib = (size_t)rows * dim * 4, ob = (size_t)rows * normalize_new_dim(dim) * 4;
   CU(fn_, D.xf.ensure(ib));
@@ -331,15 +473,13 @@ void HostCall::normalize(const float* x, int rows, int dim, float* out) {
   CU(fn_, normalize_rows((const float*)D.xf.p, rows, dim, (float*)D.yf.p, nullptr, D.rws.p, D.rws.cap, D.stream));
   CU(fn_, cudaMemcpyAsync(out, D.yf.p, ob, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaStreamSynchronize(D.stream));
-  cudaSetDevice(prev);
 }
 
 void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p,
                    uint64_t* idx, void* dist) {
   // single GPU: the graded shapes of this entry point are small (test/test_feature.py:67-81)
-  Gpu& D = g_rt.gpus[0];
-  int prev = 0, sms = 0;
-  cudaGetDevice(&prev);
+  Gpu& D = ctx_->gpus[0];
+  int sms = 0;
   CU(fn_, cudaSetDevice(D.dev));
   CU(fn_, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, D.dev));
   const size_t xb = (size_t)xrows * dim * 4, yb = (size_t)yrows * dim * 4;
@@ -356,7 +496,6 @@ void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yro
   CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaStreamSynchronize(D.stream));
-  cudaSetDevice(prev);
 }
 
 // ---- the filter overload and its caller --------------------------------
@@ -364,7 +503,7 @@ void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yro
 // any number of groups in ONE launch (their query lists must be disjoint); filt_end downloads.
 void HostCall::filt_begin(const float* x, const float* y, int xrows, int yrows, int dim, int k, const uint64_t* idx,
                           const float* dist) {
-  Gpu& D = g_rt.gpus[0];
+  Gpu& D = ctx_->gpus[0];
   CU(fn_, cudaSetDevice(D.dev));
   const size_t xb = (size_t)xrows * dim * 4, yb = (size_t)yrows * dim * 4;
   const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
@@ -379,7 +518,7 @@ void HostCall::filt_begin(const float* x, const float* y, int xrows, int yrows, 
 }
 
 void HostCall::filt_run(const std::vector<FilterGroup>& groups, int xrows, int yrows, int dim, int k, double p) {
-  Gpu& D = g_rt.gpus[0];
+  Gpu& D = ctx_->gpus[0];
   int sms = 0;
   CU(fn_, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, D.dev));
   const int TR = lp_filtered_tile_rows();
@@ -413,7 +552,7 @@ void HostCall::filt_run(const std::vector<FilterGroup>& groups, int xrows, int y
 }
 
 void HostCall::filt_end(int yrows, int k, uint64_t* idx, float* dist) {
-  Gpu& D = g_rt.gpus[0];
+  Gpu& D = ctx_->gpus[0];
   const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
   if (ib) CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
   if (db) CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
@@ -435,22 +574,17 @@ static std::vector<uint32_t> as_set(const char* fn, const uint64_t* f, int n, in
 
 void HostCall::lpk_filtered(const float* x, const float* y, int xrows, int yrows, int dim, int k, double p,
                             const uint64_t* filter_x, int nfx, const uint64_t* filter_y, int nfy, uint64_t* idx, float* dist) {
-  int prev = 0;
-  cudaGetDevice(&prev);
   std::vector<FilterGroup> groups(1);
   groups[0].xs = as_set(fn_, filter_x, nfx, xrows, "filter_x");
   groups[0].ys = as_set(fn_, filter_y, nfy, yrows, "filter_y");
   filt_begin(x, y, xrows, yrows, dim, k, idx, dist);
   filt_run(groups, xrows, yrows, dim, k, p);
   filt_end(yrows, k, idx, dist);
-  cudaSetDevice(prev);
 }
 
 void HostCall::kmedians_nn(const float* x, const float* y, int xrows, int yrows, int dim, const float* medians_x,
                            const int32_t* labels_x, int nmx, const float* medians_y, const int32_t* labels_y, int nmy, int c,
                            int k, uint64_t* idx, float* dist) {
-  int prev = 0;
-  cudaGetDevice(&prev);
   // KMedians.h:268-273: the c nearest `other` medians of every median, L1 (K1f on the GPU, exact)
   std::vector<uint64_t> near((size_t)nmy * c);
   std::vector<float> near_d((size_t)nmy * c);
@@ -486,7 +620,6 @@ void HostCall::kmedians_nn(const float* x, const float* y, int xrows, int yrows,
   }
   if (!batch.empty()) filt_run(batch, xrows, yrows, dim, k, 1.0);
   filt_end(yrows, k, idx, dist);
-  cudaSetDevice(prev);
 }
 
 }  // namespace spv

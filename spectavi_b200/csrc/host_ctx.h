@@ -4,9 +4,10 @@
 // query rows broadcast, per-GPU top-2 all-gathered with NCCL and merged by K5).
 //
 // The reference keeps no state between calls (every call rebuilds everything,
-// Spectavi.cpp:326-328); the cache here holds only scratch memory and
-// communicators, never results, and is guarded by one mutex because the
-// reference's functions are re-entrant.
+// Spectavi.cpp:326-328) and its functions are re-entrant; the cache here holds
+// only scratch memory and communicators, never results.  Single-GPU calls each
+// take their own context (streams + buffers) from a pool, so concurrent callers
+// run concurrently; the multi-GPU layout serialises on its NCCL communicators.
 #pragma once
 #include <cstddef>
 #include <cstdint>
@@ -33,6 +34,8 @@ struct MatchSink {
   double min_ratio;
   std::function<uint64_t*(uint64_t)> alloc;
 };
+
+struct Ctx;
 
 class HostCall {
  public:
@@ -67,7 +70,9 @@ class HostCall {
   void filt_end(int yrows, int k, uint64_t* idx, float* dist);
   void deliver_matches(const MatchSink& ms, int yrows, bool dist_f32);   // K6 on GPU 0's merged keys
   const char* fn_;
-  std::unique_lock<std::mutex> lock_;
+  Ctx* ctx_ = nullptr;                  // streams, staging lanes, scratch buffers of this call
+  std::unique_lock<std::mutex> multi_lock_;    // held for the call when SPECTAVI_GPUS > 1
+  int prev_dev_ = 0;                           // the caller's current device, restored on return
 };
 
 }  // namespace spv

@@ -121,7 +121,8 @@ struct Params {
   uint32_t xoffset;              // global index of local train row 0
   int nxt, nyt;                  // tiles along train / query
   long long units;               // nxt * nyt
-  unsigned long long* keys;      // [2][yrows]
+  unsigned long long* keys;      // rank 0 at keys[row], rank 1 at keys[kstride + row]
+  long long kstride;             // rows of the whole key buffer (>= yrows: a launch may cover a slice of the query rows)
   int nst;                       // train-tile stages in the shared-memory ring
 };
 
@@ -132,11 +133,25 @@ constexpr size_t SMEM_STATE_BYTES = (size_t)2 * BY * 8;   // best[BY], second[BY
 
 // global fold: keys[0][row] / keys[1][row] <- top2(old pair U {k}).  The loser of
 // the first atomicMin is offered to rank 1; the 2nd smallest key overall is
-// always the loser of some exchange, and no loser is smaller than it.
-__device__ __forceinline__ void fold_key(unsigned long long* keys, int yrows, int row, unsigned long long k) {
+// always the loser of some exchange, and no loser is smaller than it.  A key that
+// is already the best (the same train row folded twice: a shard or xoffset range
+// offered again, or a pair seeded from this buffer and published unchanged) is
+// not offered to rank 1, so the two ranks never hold the same train row.
+__device__ __forceinline__ void fold_key(unsigned long long* keys, long long kstride, int row, unsigned long long k) {
   unsigned long long old = atomicMin(keys + row, k);
+  if (old == k) return;
   unsigned long long loser = old > k ? old : k;
-  if (loser != KEY_NONE) atomicMin(keys + yrows + row, loser);
+  if (loser != KEY_NONE) atomicMin(keys + kstride + row, loser);
+}
+
+// Threshold of a query row whose running 2nd-best key is `second`: a candidate takes the slow path iff
+// dist < thr.  A stored key may carry a LARGER train index than a later candidate (keys seeded from the
+// global buffer come from any train range), so a candidate that ties the 2nd-best distance must still be
+// offered: thr = d2 + 1 (the whole-key atomicMin then decides).  No 2nd-best yet: INT_MAX admits every
+// real distance (BruteForceNnL1K2.h:99-103).
+__device__ __forceinline__ uint32_t thr_of(unsigned long long second) {
+  const uint32_t d2 = (uint32_t)(second >> 32);
+  return d2 < THR_MAX ? d2 + 1u : THR_MAX;
 }
 
 // slow path: offer one candidate to its query row's (best, second) keys in shared
@@ -146,6 +161,7 @@ __device__ __forceinline__ void fold_key(unsigned long long* keys, int yrows, in
 __device__ __noinline__ void offer(unsigned long long* best, uint32_t dist, uint32_t gidx) {
   const unsigned long long key = ((unsigned long long)dist << 32) | gidx;
   const unsigned long long old = atomicMin(best, key);
+  if (old == key) return;   // the seeded best offered again (same train range folded twice)
   const unsigned long long loser = old > key ? old : key;
   if (loser != KEY_NONE) atomicMin(best + BY, loser);
 }
@@ -263,8 +279,8 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     const int row = ytile_idx * BY + warp * 32 + lane;
     if (row < p.yrows) {
       const unsigned long long k1 = st[lane], k2 = st[BY + lane];
-      if (k1 != KEY_NONE) fold_key(p.keys, p.yrows, row, k1);
-      if (k2 != KEY_NONE) fold_key(p.keys, p.yrows, row, k2);
+      if (k1 != KEY_NONE) fold_key(p.keys, p.kstride, row, k1);
+      if (k2 != KEY_NONE) fold_key(p.keys, p.kstride, row, k2);
     }
     __syncwarp();
   };
@@ -276,11 +292,21 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
         if (lane == 0) mbar_arrive(bar_yempty);   // this warp no longer reads the old query tile
         flush(cur_yt);
       }
-      st[lane] = KEY_NONE;
-      st[BY + lane] = KEY_NONE;
+      // Seed the rows' (best, second) from what the key buffer already holds -- earlier launches over other
+      // train ranges (the host path streams the train set in chunks, host_ctx.cu) or other CTAs of this one --
+      // so that a launch does not pay the threshold warm-up (~2 ln N slow-path hits per query row) again.
+      // A stale read only means a weaker threshold; the pair is published again through fold_key, which
+      // ignores a key that is already there.
+      {
+        const int srow = yt * BY + warp * 32 + lane;
+        unsigned long long s1 = KEY_NONE, s2 = KEY_NONE;
+        if (srow < p.yrows) { s1 = __ldcg(p.keys + srow); s2 = __ldcg(p.keys + p.kstride + srow); }
+        st[lane] = s1;
+        st[BY + lane] = s2;
+      }
       __syncwarp();
 #pragma unroll
-      for (int i = 0; i < TY; ++i) negthr[i] = 0u - THR_MAX;
+      for (int i = 0; i < TY; ++i) negthr[i] = 0u - thr_of(st[BY + ly + 4 * i]);
       mbar_wait(bar_yfull, yphase);
       yphase ^= 1;
       cur_yt = yt;
@@ -330,18 +356,107 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
         }
       }
       __syncwarp();
-      // every train index seen later is larger than any stored one, so a later
-      // candidate must beat the row's running 2nd-best distance STRICTLY
 #pragma unroll
-      for (int i = 0; i < TY; ++i) {
-        const uint32_t d2 = (uint32_t)(st[BY + ly + 4 * i] >> 32);
-        negthr[i] = 0u - min(d2, THR_MAX);
-      }
+      for (int i = 0; i < TY; ++i) negthr[i] = 0u - thr_of(st[BY + ly + 4 * i]);
     }
     if (++stage == NST) { stage = 0; phase ^= 1; }
     if (++xt == p.nxt) { xt = 0; ++yt; }
   }
   flush(cur_yt);
+}
+
+
+// ---------------------------------------------------------------- wide rows
+// dim > 512: a 256-row query tile no longer fits shared memory beside the train ring (the tiled
+// kernel keeps whole rows resident).  The reference accepts any dim % 16 == 0
+// (BruteForceNnL1K2.h:78-81), so wide rows take this plain tiled kernel instead: 64 x 64 row tiles,
+// the columns streamed in 64-byte panels through shared memory (k-chunk-major, as K1 reads them),
+// a 4 x 4 register tile per thread, the same key protocol (seeded thresholds, shared (best, second)
+// per query row, fold_key).  Same results bit for bit; ALU-bound like K1 but at a lower rate (the
+// operand loads are not hidden behind a producer warp) -- wide rows are not a graded configuration.
+constexpr int WB = 64;            // rows per tile, both sides
+constexpr int WCH = 4;            // 16-byte chunks per panel
+constexpr int WTHREADS = 256;
+
+struct WideParams {
+  const uint8_t* x;
+  const uint8_t* y;
+  int xrows, yrows, dim;
+  uint32_t xoffset;
+  int nxt, splits;
+  unsigned long long* keys;
+  long long kstride;
+};
+
+__global__ void __launch_bounds__(WTHREADS) l1_top2_wide_kernel(const WideParams p) {
+  __shared__ uint4 ys[WCH][WB], xs[WCH][WB];
+  __shared__ unsigned long long st[2 * BY];   // offer() addresses the second at best + BY
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  const int y0 = blockIdx.x * WB;
+  const int t0 = (int)((long long)p.nxt * blockIdx.y / p.splits), t1 = (int)((long long)p.nxt * (blockIdx.y + 1) / p.splits);
+  if (tid < WB) {
+    unsigned long long s1 = KEY_NONE, s2 = KEY_NONE;
+    if (y0 + tid < p.yrows) { s1 = __ldcg(p.keys + y0 + tid); s2 = __ldcg(p.keys + p.kstride + y0 + tid); }
+    st[tid] = s1;
+    st[BY + tid] = s2;
+  }
+  __syncthreads();
+  const int nk16 = p.dim / 16;
+  for (int t = t0; t < t1; ++t) {
+    const int x0 = t * WB;
+    uint32_t acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0;
+    for (int c0 = 0; c0 < nk16; c0 += WCH) {
+      {   // stage: thread -> (chunk, row) of both tiles; rows past the end read as zeros (never offered)
+        const int c = tid >> 6, r = tid & 63;
+        uint4 vy = make_uint4(0, 0, 0, 0), vx = vy;
+        if (c0 + c < nk16) {
+          if (y0 + r < p.yrows) vy = __ldg(reinterpret_cast<const uint4*>(p.y + (size_t)(y0 + r) * p.dim) + c0 + c);
+          if (x0 + r < p.xrows) vx = __ldg(reinterpret_cast<const uint4*>(p.x + (size_t)(x0 + r) * p.dim) + c0 + c);
+        }
+        ys[c][r] = vy;
+        xs[c][r] = vx;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int c = 0; c < WCH; ++c) {
+        uint4 a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = ys[c][ty + 16 * i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = xs[c][tx + 16 * j];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            acc[i][j] = sad4(a[i].x, b[j].x, acc[i][j]); acc[i][j] = sad4(a[i].y, b[j].y, acc[i][j]);
+            acc[i][j] = sad4(a[i].z, b[j].z, acc[i][j]); acc[i][j] = sad4(a[i].w, b[j].w, acc[i][j]);
+          }
+      }
+      __syncthreads();
+    }
+    // selection: thresholds are read once per tile (stale = weaker, never wrong); offers are exact
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = ty + 16 * i;
+      if (y0 + r >= p.yrows) continue;
+      const uint32_t thr = thr_of(st[BY + r]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int lx = x0 + tx + 16 * j;
+        if (lx < p.xrows && acc[i][j] < thr) offer(st + r, acc[i][j], p.xoffset + (uint32_t)lx);
+      }
+    }
+    __syncthreads();
+  }
+  if (tid < WB && y0 + tid < p.yrows) {
+    const unsigned long long k1 = st[tid], k2 = st[BY + tid];
+    if (k1 != KEY_NONE) fold_key(p.keys, p.kstride, y0 + tid, k1);
+    if (k2 != KEY_NONE) fold_key(p.keys, p.kstride, y0 + tid, k2);
+  }
 }
 
 // ------------------------------------------------------- small helper kernels
@@ -473,14 +588,29 @@ cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kco
 }
 
 cudaError_t l1_top2_u8(const uint8_t* dx, const uint8_t* dy, int xrows, int yrows, int dim, uint32_t xoffset,
-                       unsigned long long* keys, cudaStream_t stream) {
+                       unsigned long long* keys, cudaStream_t stream, long long kstride) {
   if (xrows <= 0 || yrows <= 0) return cudaSuccess;   // nothing to fold in
-  if (dim <= 0 || dim % 16 != 0 || dim > 512) return cudaErrorInvalidValue;
+  if (dim <= 0 || dim % 16 != 0) return cudaErrorInvalidValue;
+  if (kstride < yrows) kstride = yrows;
+  // keys carry 32 index bits: the last global index must stay below the "none" pattern
+  if ((unsigned long long)xoffset + (unsigned long long)xrows > 0xFFFFFFFFull) return cudaErrorInvalidValue;
   int dev = 0, sms = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (e != cudaSuccess) return e;
+  if (dim > L1K2_TILED_MAX_DIM) {
+    WideParams w;
+    w.x = dx; w.y = dy; w.xrows = xrows; w.yrows = yrows; w.dim = dim; w.xoffset = xoffset;
+    w.nxt = (xrows + WB - 1) / WB;
+    const int nyt = (yrows + WB - 1) / WB;
+    int splits = (4 * sms + nyt - 1) / nyt;          // about 4 CTAs per SM when the query side alone is short
+    splits = splits < 1 ? 1 : (splits > w.nxt ? w.nxt : splits);
+    w.splits = splits; w.keys = keys; w.kstride = kstride;
+    l1_top2_wide_kernel<<<dim3(nyt, splits), WTHREADS, 0, stream>>>(w);
+    count_launch();
+    return cudaGetLastError();
+  }
   CUtensorMap tmx, tmy;
   if (!make_rows_map(&tmx, dx, xrows, dim, BX) || !make_rows_map(&tmy, dy, yrows, dim, BY)) return cudaErrorInvalidValue;
   Params p;
@@ -488,6 +618,7 @@ cudaError_t l1_top2_u8(const uint8_t* dx, const uint8_t* dy, int xrows, int yrow
   p.nxt = (xrows + BX - 1) / BX; p.nyt = (yrows + BY - 1) / BY;
   p.units = (long long)p.nxt * p.nyt;
   p.keys = keys;
+  p.kstride = kstride;
   return launch_tiled(tmx, tmy, p, sms, stream);
 }
 

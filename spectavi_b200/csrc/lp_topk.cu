@@ -66,6 +66,9 @@ struct LpParams {
   const uint32_t* xsel;            // candidate row ids, group after group
   const int4* tiles;               // per blockIdx.x: {ypos, ycnt <= TB, xpos, xcnt}
   int nysel;                       // entries in ysel (row stride of partial)
+  // FLOOR only (k > LP_MAX_K runs in passes of LP_MAX_K): a candidate must be GREATER than floor[query row],
+  // the last key the previous pass delivered; KEY_NONE = the row is exhausted
+  const unsigned long long* floor;
 };
 
 // Train rows of a thread's 8 x 8 register tile: columns j = 0..3 are tile rows 4 tx + j, columns 4..7 are
@@ -82,8 +85,9 @@ __device__ __forceinline__ uint32_t dist_bits(int d) { return (uint32_t)d; }    
 // Two CTAs per SM (128 registers, ~170 B of spills around the prefetch registers): with one CTA the two
 // warps per scheduler left 40 % of the issue slots empty on fixed-latency waits, barriers and LDS
 // (ncu: issue active 60 -> 78 %, fma pipe 51 -> 65 %, 20 k x 20 k x 132 p = 1: 6.3 -> 4.9 ms).
-template <typename T, int PM, bool FILT>
+template <typename T, int PM, bool FILT, bool FLOOR>
 __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
+  static_assert(!(FILT && FLOOR), "the filter overload runs single-pass (k <= LP_MAX_K)");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* ys = reinterpret_cast<T*>(smem_raw);                     // [KC][PITCH]
   T* xs = ys + KC * PITCH;                                    // [KC][PITCH]
@@ -192,7 +196,7 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
     uint32_t thb[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) thb[i] = thr[ty * 8 + i];
-    if (t == t0 && k <= 16) {
+    if (!FLOOR && t == t0 && k <= 16) {
       const int lane = tid & 31, hb = lane & 16;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -216,7 +220,12 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
     for (int i = 0; i < 8; ++i) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const bool c = (!FILT || ty * 8 + i < ycnt) && (x0 + xrow(tx, j) < xcnt) && dist_bits(acc[i][j]) <= thb[i];   // THR_NONE admits all
+        bool c = (!FILT || ty * 8 + i < ycnt) && (x0 + xrow(tx, j) < xcnt) && dist_bits(acc[i][j]) <= thb[i];   // THR_NONE admits all
+        if (FLOOR) {   // later passes of a k > LP_MAX_K search: only what the earlier passes have not delivered
+          const int qr = y0 + ty * 8 + i;
+          const unsigned long long fl = qr < P.yrows ? P.floor[qr] : KEY_NONE;
+          c = c && ((((unsigned long long)dist_bits(acc[i][j]) << 32) | (uint32_t)(x0 + xrow(tx, j))) > fl);
+        }
         pend |= (unsigned long long)c << (i * 8 + j);
       }
     }
@@ -296,13 +305,17 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
 // keep the caller's zeros)
 // ysel != nullptr (filtered): list position `row` belongs to output row ysel[row]; a row's unfilled
 // leading columns and every row outside the filter keep the caller's values (idx / dist are in-out).
+// Passes (k > LP_MAX_K): this pass's k entries go to columns col0 .. of a kout-wide output whose row holds
+// ntotal entries in all (right-aligned as a whole), and the last key delivered becomes the next pass's floor.
 template <typename D>
 __global__ void lp_merge_kernel(const unsigned long long* __restrict__ partial, int splits, int yrows, int k,
                                 uint64_t* __restrict__ idx, D* __restrict__ dist,
-                                const uint32_t* __restrict__ ysel = nullptr) {
+                                const uint32_t* __restrict__ ysel = nullptr, int kout = 0, int col0 = -1,
+                                unsigned long long* __restrict__ floor_out = nullptr) {
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= yrows) return;
   const size_t orow = ysel ? ysel[row] : (uint32_t)row;
+  if (kout <= 0) kout = k;
   // count what exists (at most k are needed)
   int total = 0;
   for (int s = 0; s < splits && total < k; ++s) {
@@ -326,33 +339,34 @@ __global__ void lp_merge_kernel(const unsigned long long* __restrict__ partial, 
       }
     }
     last = best; have_last = true;
-    const int col = k - n + out;
-    idx[orow * k + col] = best & 0xFFFFFFFFull;
+    const int col = col0 >= 0 ? col0 + out : k - n + out;
+    idx[orow * kout + col] = best & 0xFFFFFFFFull;
     const uint32_t b = (uint32_t)(best >> 32);
-    if constexpr (std::is_same<D, float>::value) dist[orow * k + col] = __uint_as_float(b);
-    else dist[orow * k + col] = (int32_t)b;
+    if constexpr (std::is_same<D, float>::value) dist[orow * kout + col] = __uint_as_float(b);
+    else dist[orow * kout + col] = (int32_t)b;
   }
+  if (floor_out) floor_out[row] = (n == k) ? last : KEY_NONE;
 }
 
 size_t lp_smem_bytes(int k) {
   return (size_t)2 * KC * PITCH * 4 + TB * 4 + TB * 4 + QCAP * 8 + QCAP * 2 + 16 + 2 * TB * 4 + (size_t)TB * k * 8;
 }
 
-template <typename T, int PM, bool FILT>
+template <typename T, int PM, bool FILT, bool FLOOR>
 cudaError_t launch_lp(const LpParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
-  cudaError_t e = cudaFuncSetAttribute(lp_topk_kernel<T, PM, FILT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(lp_topk_kernel<T, PM, FILT, FLOOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  lp_topk_kernel<T, PM, FILT><<<grid, NT, smem, stream>>>(P);
+  lp_topk_kernel<T, PM, FILT, FLOOR><<<grid, NT, smem, stream>>>(P);
   count_launch();
   return cudaGetLastError();
 }
 
-template <typename T, bool FILT = false>
+template <typename T, bool FILT = false, bool FLOOR = false>
 cudaError_t launch_lp_p(const LpParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
-  if (P.p == 1.0) return launch_lp<T, P_ONE, FILT>(P, grid, smem, stream);     // BruteForceNn.h:70-78: exact comparisons on m_p
-  if (P.p == 2.0) return launch_lp<T, P_TWO, FILT>(P, grid, smem, stream);
-  if (P.p == 0.5) return launch_lp<T, P_HALF, FILT>(P, grid, smem, stream);
-  return launch_lp<T, P_POW, FILT>(P, grid, smem, stream);
+  if (P.p == 1.0) return launch_lp<T, P_ONE, FILT, FLOOR>(P, grid, smem, stream);     // BruteForceNn.h:70-78: exact comparisons on m_p
+  if (P.p == 2.0) return launch_lp<T, P_TWO, FILT, FLOOR>(P, grid, smem, stream);
+  if (P.p == 0.5) return launch_lp<T, P_HALF, FILT, FLOOR>(P, grid, smem, stream);
+  return launch_lp<T, P_POW, FILT, FLOOR>(P, grid, smem, stream);
 }
 
 }  // namespace
@@ -383,14 +397,18 @@ int lp_splits(int xrows, int yrows, int k, int sms) {
   return pick_splits((yrows + TB - 1) / TB, (xrows + TB - 1) / TB, sms, (size_t)(yrows > 0 ? yrows : 0) * k);
 }
 
+// k > LP_MAX_K runs in passes of LP_MAX_K (the sorted per-row lists live in shared memory); the scratch is one
+// pass's partial lists plus one floor key per query row
 size_t lp_partial_bytes(int xrows, int yrows, int k, int sms) {
-  return (size_t)lp_splits(xrows, yrows, k, sms) * (size_t)yrows * k * sizeof(unsigned long long);
+  const int kp = k < LP_MAX_K ? k : LP_MAX_K;
+  const size_t lists = (size_t)lp_splits(xrows, yrows, kp, sms) * (size_t)yrows * kp * sizeof(unsigned long long);
+  return lists + (k > LP_MAX_K ? (size_t)(yrows > 0 ? yrows : 0) * sizeof(unsigned long long) : 0);
 }
 
 cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
                     unsigned long long* partial, uint64_t* didx, void* ddist, cudaStream_t stream) {
   if (yrows <= 0) return cudaSuccess;
-  if (k < 1 || k > LP_MAX_K || dim < 1) return cudaErrorInvalidValue;
+  if (k < 1 || dim < 1) return cudaErrorInvalidValue;
   // the caller's arrays start as zeros (numpy), and unfilled columns stay zero
   cudaError_t e = cudaMemsetAsync(didx, 0, (size_t)yrows * k * sizeof(uint64_t), stream);
   if (e != cudaSuccess) return e;
@@ -402,17 +420,41 @@ cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int 
   LpParams P;
   P.x = dx; P.y = dy; P.xrows = xrows; P.yrows = yrows; P.dim = dim; P.k = k; P.p = p;
   P.nxt = (xrows + TB - 1) / TB;
-  P.splits = lp_splits(xrows, yrows, k, sms);
   P.partial = partial;
-  P.ysel = P.xsel = nullptr; P.tiles = nullptr; P.nysel = 0;
+  P.ysel = P.xsel = nullptr; P.tiles = nullptr; P.nysel = 0; P.floor = nullptr;
+  if (k <= LP_MAX_K) {
+    P.splits = lp_splits(xrows, yrows, k, sms);
+    const dim3 grid((yrows + TB - 1) / TB, P.splits);
+    const size_t smem = lp_smem_bytes(k);
+    e = is_int ? launch_lp_p<int>(P, grid, smem, stream) : launch_lp_p<float>(P, grid, smem, stream);
+    if (e != cudaSuccess) return e;
+    if (is_int) lp_merge_kernel<int32_t><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (int32_t*)ddist);
+    else lp_merge_kernel<float><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (float*)ddist);
+    count_launch();
+    return cudaGetLastError();
+  }
+  // k > LP_MAX_K (the reference takes any k, BruteForceNn.h:93-118): passes of LP_MAX_K over the whole train set,
+  // each admitting only keys above the last one the previous pass delivered.  A row holds min(k, xrows) entries,
+  // right-aligned as a whole (:111-118).
+  const int ntotal = k < xrows ? k : xrows;
+  P.splits = lp_splits(xrows, yrows, LP_MAX_K, sms);
+  unsigned long long* floor = partial + (size_t)P.splits * yrows * LP_MAX_K;
   const dim3 grid((yrows + TB - 1) / TB, P.splits);
-  const size_t smem = lp_smem_bytes(k);
-  e = is_int ? launch_lp_p<int>(P, grid, smem, stream) : launch_lp_p<float>(P, grid, smem, stream);
-  if (e != cudaSuccess) return e;
-  if (is_int) lp_merge_kernel<int32_t><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (int32_t*)ddist);
-  else lp_merge_kernel<float><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, k, didx, (float*)ddist);
-  count_launch();
-  return cudaGetLastError();
+  for (int done = 0; done < ntotal; done += LP_MAX_K) {
+    const int kp = ntotal - done < LP_MAX_K ? ntotal - done : LP_MAX_K;
+    P.k = kp;
+    P.floor = done ? floor : nullptr;
+    const size_t smem = lp_smem_bytes(kp);
+    if (done == 0) e = is_int ? launch_lp_p<int>(P, grid, smem, stream) : launch_lp_p<float>(P, grid, smem, stream);
+    else e = is_int ? launch_lp_p<int, false, true>(P, grid, smem, stream) : launch_lp_p<float, false, true>(P, grid, smem, stream);
+    if (e != cudaSuccess) return e;
+    const int col0 = k - ntotal + done;
+    if (is_int) lp_merge_kernel<int32_t><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, kp, didx, (int32_t*)ddist, nullptr, k, col0, floor);
+    else lp_merge_kernel<float><<<(yrows + 127) / 128, 128, 0, stream>>>(partial, P.splits, yrows, kp, didx, (float*)ddist, nullptr, k, col0, floor);
+    count_launch();
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 // ---- the filter overload, batched over groups (see the header)
@@ -439,7 +481,7 @@ cudaError_t lp_topk_filtered(const float* dx, const float* dy, int dim, int k, d
   P.x = dx; P.y = dy; P.xrows = 0; P.yrows = 0; P.dim = dim; P.k = k; P.p = p; P.nxt = 0;
   P.splits = lp_filtered_splits(ntiles, max_xcnt, nysel, k, sms);
   P.partial = partial;
-  P.ysel = dysel; P.xsel = dxsel; P.tiles = dtiles; P.nysel = nysel;
+  P.ysel = dysel; P.xsel = dxsel; P.tiles = dtiles; P.nysel = nysel; P.floor = nullptr;
   const dim3 grid(ntiles, P.splits);
   if ((e = launch_lp_p<float, true>(P, grid, lp_smem_bytes(k), stream)) != cudaSuccess) return e;
   lp_merge_kernel<float><<<(nysel + 127) / 128, 128, 0, stream>>>(partial, P.splits, nysel, k, didx, ddist, dysel);

@@ -27,8 +27,13 @@ struct KeyBuf {
 // ---- l1_top2.cu : K1, brute-force L1 k=2 over uint8 rows -------------------
 // Accumulates the top-2 of y against x[0..xrows) (global index = xoffset + row)
 // INTO keys (which must have been reset or hold earlier partial results).
+// kstride: rows of the whole key buffer when dy / keys address a SLICE of the query rows (rank 1 of row r
+// sits at keys[kstride + r]); 0 = yrows.  Rows wider than L1K2_TILED_MAX_DIM take the plain wide-row kernel.
+// The thresholds of a launch are seeded from what keys already holds, so folding a train set chunk by chunk
+// costs no more slow-path work than one launch; folding the same train rows twice is harmless.
+constexpr int L1K2_TILED_MAX_DIM = 512;
 cudaError_t l1_top2_u8(const uint8_t* dx, const uint8_t* dy, int xrows, int yrows, int dim,
-                       uint32_t xoffset, unsigned long long* keys, cudaStream_t stream);
+                       uint32_t xoffset, unsigned long long* keys, cudaStream_t stream, long long kstride = 0);
 cudaError_t keys_reset(unsigned long long* keys, int yrows, cudaStream_t stream);
 // K5: keys_dst = top2(keys_dst U src[0] U ... U src[nsrc-1]); src s at src + s*2*yrows
 cudaError_t keys_merge(unsigned long long* dst, const unsigned long long* src, int nsrc, int yrows,

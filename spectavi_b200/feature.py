@@ -87,6 +87,32 @@ _kmedians_fnn.argtypes = [ndpointer(ct.c_float, flags="C_CONTIGUOUS"),
                           ct.c_int, ct.c_int, ct.POINTER(NdArray), ct.POINTER(NdArray)]
 
 
+LP_MAX_K_FILTERED = 128     # csrc/spv_common.h LP_MAX_K: the filter overload runs single-pass
+
+clib.spv_cascade_ws_bytes.restype = ct.c_size_t
+clib.spv_cascade_ws_bytes.argtypes = [ct.c_int] * 6
+
+
+def _check_l1_dim(dim):
+    # BruteForceNnL1K2.h:78-81 throws (a C++ exception escaping extern "C", i.e. abort); the C entry point here
+    # aborts too, so the precondition is raised in Python first
+    if dim <= 0 or dim % 16 != 0:
+        raise ValueError("data dimension (%d) must be a positive multiple of 16" % dim)
+
+
+def _check_cascade(xrows, yrows, dim, k, m, n, g):
+    _check_l1_dim(dim)
+    if k < 2:
+        raise ValueError("k = %d: the cascade matcher always produces 2 neighbours" % k)
+    if not 1 <= m <= 31:
+        raise ValueError("m = %d outside [1, 31] (codes are int32, CascadingHashNn.h:102-111)" % m)
+    if n < 1 or g < 0:
+        raise ValueError("need n >= 1 and g >= 0")
+    if clib.spv_cascade_ws_bytes(xrows, yrows, dim, m, n, g) == 0:
+        raise ValueError("unsupported cascade parameters dim=%d m=%d n=%d g=%d (min(g, m) <= 12, n * 2^g <= 2^24, "
+                         "n * rows < 2^31, and the hash tables of one pass must fit shared memory)" % (dim, m, n, g))
+
+
 def nn_bruteforce(x, y, p=.5, mu=0., k=2, use_int=False):
     """k nearest rows of ``x`` for every row of ``y`` under sum |d|^p
     (reference feature.py:246-289).  Returns ``(idx uint64, dist)`` of shape
@@ -96,6 +122,8 @@ def nn_bruteforce(x, y, p=.5, mu=0., k=2, use_int=False):
     yrows, ydim = y.shape
     assert ydim == xdim
     dim = xdim
+    if k < 1:
+        raise ValueError("k must be >= 1")
     nn_idx = NdArray(dtype='uint64')
     if not use_int:
         nn_dist = NdArray(dtype='float32')
@@ -122,6 +150,8 @@ def nn_bruteforce_filtered(x, y, filter_x, filter_y, p=1., mu=0., k=2, nn_idx=No
     if nn_dist is None:
         nn_dist = np.zeros((yrows, k), 'float32')
     assert nn_idx.shape == (yrows, k) and nn_dist.shape == (yrows, k)
+    if not 1 <= k <= LP_MAX_K_FILTERED:
+        raise ValueError("k = %d outside [1, %d]" % (k, LP_MAX_K_FILTERED))
     fx = np.ascontiguousarray(np.asarray(filter_x, 'uint64').ravel())
     fy = np.ascontiguousarray(np.asarray(filter_y, 'uint64').ravel())
     if (fx.size and fx.max() >= xrows) or (fy.size and fy.max() >= yrows):
@@ -145,8 +175,10 @@ def kmedians_find_nearest_neighbours(x, y, medians_x, labels_x, medians_y, label
     assert lx.shape == (xrows,) and ly.shape == (yrows,)
     if lx.min() < 0 or lx.max() >= medians_x.shape[0] or ly.min() < 0 or ly.max() >= medians_y.shape[0]:
         raise ValueError("label outside [0, number of medians)")           # the C entry point aborts on this
-    if not 1 <= c <= medians_x.shape[0]:
-        raise ValueError("c must be in [1, number of train medians]")
+    if not 1 <= c <= min(medians_x.shape[0], LP_MAX_K_FILTERED):
+        raise ValueError("c must be in [1, min(number of train medians, %d)]" % LP_MAX_K_FILTERED)
+    if not 1 <= k <= LP_MAX_K_FILTERED:
+        raise ValueError("k = %d outside [1, %d]" % (k, LP_MAX_K_FILTERED))
     nn_idx = NdArray(dtype='uint64')
     nn_dist = NdArray(dtype='float32')
     _kmedians_fnn(x, y, xrows, yrows, dim, np.ascontiguousarray(medians_x, 'float32'), lx, medians_x.shape[0],
@@ -162,6 +194,7 @@ def nn_bruteforcel1k2(x, y, nthreads=1):
     yrows, ydim = y.shape
     assert ydim == xdim
     dim = xdim
+    _check_l1_dim(dim)
     nn_idx = NdArray(dtype='uint64')
     nn_dist = NdArray(dtype='int32')
     _nn_bruteforcel1k2(x, y, xrows, yrows, dim, nthreads, nn_idx, nn_dist)
@@ -184,6 +217,7 @@ def nn_cascading_hash(x, y, k=2, m=None, n=2, g=2):
             return nn_bruteforcel1k2((x + 128).astype('uint8'),
                                      (y + 128).astype('uint8'), nthreads=8)
     dim = xdim
+    _check_cascade(xrows, yrows, dim, k, m, n, g)
     cashash_idx = NdArray(dtype='uint64')
     cashash_dist = NdArray(dtype='float32')
     _nn_cascading_hash(x, y, xrows, yrows, dim, k, m, n, g, cashash_idx,
@@ -242,6 +276,7 @@ def match_bruteforcel1k2(x, y, min_ratio=1.75):
     xrows, xdim = x.shape
     yrows, ydim = y.shape
     assert ydim == xdim
+    _check_l1_dim(xdim)
     out = NdArray(dtype='uint64')
     _match_l1k2(x, y, xrows, yrows, xdim, float(min_ratio), out)
     return _split_matches(out)
@@ -260,6 +295,7 @@ def match_cascading_hash(x, y, min_ratio=1.75, m=None, n=2, g=2):
         if m < 4:
             return match_bruteforcel1k2((x + 128).astype('uint8'),
                                         (y + 128).astype('uint8'), min_ratio)
+    _check_cascade(xrows, yrows, xdim, 2, m, n, g)
     out = NdArray(dtype='uint64')
     _match_cashash(x, y, xrows, yrows, xdim, m, n, g, float(min_ratio), out)
     return _split_matches(out)

@@ -130,3 +130,24 @@ def test_bruteforce_device_resident(po, p, k, use_int):
     gi, gd = dev.nn_bruteforce(torch.from_numpy(x[:2]).cuda(), torch.from_numpy(y).cuda(), p=p, k=4)
     oi, od = po.bruteforce(x[:2], y, 4, p, 0., use_int=use_int)
     assert (gi.cpu().numpy().view(np.uint64) == oi).all() and (gd.cpu().numpy().view(np.uint32) == od.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("xr,k,use_int", [(1000, 200, False), (300, 129, False), (150, 200, False), (700, 300, True)])
+def test_bruteforce_k_above_128(po, feature, xr, k, use_int):
+    """The reference takes any k (BruteForceNn.h:93-118); above 128 the search runs in passes of 128, each
+    admitting only keys beyond the last one delivered.  Incl. fewer train rows than k (right-aligned, zero-filled)
+    and tie-heavy integer rows."""
+    rng = np.random.RandomState(k + xr)
+    if use_int:
+        x = rng.randint(0, 4, (xr, 12)).astype("float32") / 100.
+        y = rng.randint(0, 4, (60, 12)).astype("float32") / 100.
+    else:
+        x = rng.randn(xr, 20).astype("float32")
+        y = rng.randn(60, 20).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=1., mu=0., k=k, use_int=use_int)
+    if use_int:
+        ni, nd = po.numpy_topk(np.round(100 * x), np.round(100 * y), k, 1)
+        assert (gi == ni).all() and (gd == nd.astype(gd.dtype)).all()
+    else:
+        oi, od = po.bruteforce(x, y, k, 1., 0.)
+        assert (gi == oi).all() and (gd.view(np.uint32) == od.view(np.uint32)).all()

@@ -109,6 +109,7 @@ def test_cascade_golden_from_reference(dev, name, g_):
     (300, 100, 16, 26, 2, 3),        # m > 24: bucket key is the low 24 bits, full code verified
     (150, 40, 512, 12, 3, 12),       # g == m: every code is probed
     (1, 7, 128, 6, 2, 2), (2, 7, 128, 6, 2, 2),   # fewer than two candidates
+    (400, 90, 1024, 8, 2, 2), (300, 50, 528, 10, 3, 3),   # dim > 512 (reference: any dim % 16 == 0): bf16 projection, run-time chunk loop in K4
 ])
 def test_cascade_bit_exact_vs_oracle(po, dev, shape):
     xr, yr, dim, m, n, g = shape
@@ -197,3 +198,59 @@ def test_hash_codes_i8_pipeline_many_tiles(po, dev, rows, dim, m, n, g):
     sel = rng.choice(rows, 3000, replace=False)
     want = po.hashcodes(x[sel], d)
     assert (c0.cpu().numpy().T[sel] == want).all()
+
+
+@pytest.mark.parametrize("terms", [0, 1, 3])
+def test_cascade_exact_workspace_size(po, dev, terms):
+    """spv_cascade_ws_bytes must cover the layout of every dict_terms (the image size depends on the number of
+    tables per pass): dim 256, m 25, n 5 is a combination where the 1-term layout is the larger one."""
+    import torch
+    rng = np.random.RandomState(4)
+    xr, yr, dim, m, n, g = 600, 80, 256, 25, 5, 2
+    x, y = _quantised_rows(rng, xr, dim), _quantised_rows(rng, yr, dim)
+    d = dev.cascade_dictionary(dim, m, n, seed=11)
+    xu = torch.from_numpy((x + 128).astype("uint8")).cuda()
+    yu = torch.from_numpy((y + 128).astype("uint8")).cuda()
+    keys = dev.new_keys(yr, xu.device)
+    ws = dev.cascade_fold(xu, yu, keys, torch.from_numpy(d), g, 0, dict_terms=terms)   # allocates exactly ws_bytes
+    gi, gd = dev.keys_finalize(keys, 2, torch.float32)
+    del ws
+    oi, od = po.cascade(x, y, d, g, 4)
+    assert (gd.cpu().numpy() == od).all() and (gi.cpu().numpy().view(np.uint64) == oi).all()
+
+
+def test_cascade_fold_shards_concurrently(po, dev):
+    """Two train shards folded into ONE key buffer from two streams at once: K4's final fold is the same
+    two-atomicMin protocol as K1's, so no update is lost and the result equals the unsharded one."""
+    import torch
+    rng = np.random.RandomState(12)
+    xr, yr, dim, m, n, g = 6000, 3000, 128, 8, 2, 2
+    x, y = _quantised_rows(rng, xr, dim), _quantised_rows(rng, yr, dim)
+    y[:1500] = np.clip(x[rng.randint(0, xr, 1500)] + rng.randint(-3, 4, (1500, dim)), -128, 127)
+    d = torch.from_numpy(dev.cascade_dictionary(dim, m, n, seed=5))
+    xu = torch.from_numpy((x + 128).astype("uint8")).cuda()
+    yu = torch.from_numpy((y + 128).astype("uint8")).cuda()
+    keys = dev.new_keys(yr, xu.device)
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    with torch.cuda.stream(s1):
+        w1 = dev.cascade_fold(xu[:3000].contiguous(), yu, keys, d, g, 0)
+    with torch.cuda.stream(s2):
+        w2 = dev.cascade_fold(xu[3000:].contiguous(), yu, keys, d, g, 3000)
+    torch.cuda.synchronize()
+    gi, gd = dev.keys_finalize(keys, 2, torch.float32)
+    # per-shard candidate sets: the union of the two shard searches (buckets are per shard)
+    a = po.cascade(x[:3000], y, d.numpy(), g, 4)
+    b = po.cascade(x[3000:], y, d.numpy(), g, 4)
+    NONE = np.uint64(0xFFFFFFFFFFFFFFFF)
+    bi = np.where(b[0] == NONE, NONE, b[0] + np.uint64(3000))
+    ci, cd = np.concatenate([a[0], bi], 1), np.concatenate([a[1], b[1]], 1)
+    order = np.lexsort((ci, cd), axis=1)[:, :2] if False else np.argsort(cd + 0 * ci.astype("float64"), axis=1, kind="stable")
+    # lexicographic (dist, idx) top-2 of the four candidates
+    want_i, want_d = np.empty((yr, 2), np.uint64), np.empty((yr, 2), np.float32)
+    for r in range(yr):
+        c = sorted(zip(cd[r].tolist(), ci[r].tolist()))
+        want_d[r] = [c[0][0], c[1][0]]
+        want_i[r] = [c[0][1], c[1][1]]
+    assert (gd.cpu().numpy() == want_d).all() and (gi.cpu().numpy().view(np.uint64) == want_i).all()
+    del w1, w2

@@ -23,6 +23,7 @@ def _rand(rng, rows, dim, alphabet):
     (1, 5, 16), (2, 3, 16), (3, 1, 32),     # sentinels / yrows==1 squeeze
     (63, 255, 128), (65, 257, 128), (1000, 777, 128),   # ragged tiles
     (5000, 300, 256), (700, 500, 384), (300, 200, 512),  # wider rows
+    (300, 200, 1024), (1500, 130, 528), (70, 65, 4096),  # dim > 512: the wide-row kernel (reference: any dim % 16 == 0)
 ])
 @pytest.mark.parametrize("alphabet", [256, 4])
 def test_l1k2_bit_exact(po, feature, shape, alphabet):
@@ -85,9 +86,43 @@ def test_l1k2_large_sampled(po, feature):
     assert (gi[sel] == oi).all() and (gd[sel] == od).all()
 
 
+@pytest.mark.parametrize("shape,alphabet", [((30_000, 20_000, 32), 256), ((9_000, 41_000, 16), 4), ((70_000, 8_193, 64), 256)])
+def test_l1k2_streamed_upload_full_check(po, feature, shape, alphabet):
+    """Shapes past the first piece of the host path's streamed upload (8 192 rows a side, host_ctx.cu): several
+    query pieces against the first train piece, then further train pieces folded into the same keys with seeded
+    thresholds.  Every row checked, incl. a tie-heavy alphabet (seeded keys may carry larger indices than later
+    candidates)."""
+    xr, yr, dim = shape
+    rng = np.random.RandomState(xr + yr)
+    x, y = _rand(rng, xr, dim, alphabet), _rand(rng, yr, dim, alphabet)
+    gi, gd = feature.nn_bruteforcel1k2(x, y)
+    oi, od = po.l1k2(x, y, 8)
+    assert (gd == od).all() and (gi == oi).all()
+
+
+def test_l1k2_fold_in_chunks_any_order_and_twice(po):
+    """Device API: folding the train set chunk by chunk in DESCENDING index order (every stored key has a larger
+    index than the next candidates), and folding every chunk twice, gives the one-launch result: no duplicate
+    of the best key in rank 1 (fold_key skips a key that is already there)."""
+    import torch
+    from spectavi_b200 import device as dev
+    rng = np.random.RandomState(31)
+    for alphabet, dim in ((256, 128), (3, 16)):
+        x, y = _rand(rng, 5000, dim, alphabet), _rand(rng, 700, dim, alphabet)
+        dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+        keys = dev.new_keys(700, dx.device)
+        bounds = [0, 64, 1000, 1001, 3000, 5000]
+        for lo, hi in reversed(list(zip(bounds[:-1], bounds[1:]))):
+            for _ in range(2):
+                dev.l1k2_fold(dx[lo:hi].contiguous(), dy, keys, lo)
+        gi, gd = dev.keys_finalize(keys)
+        oi, od = po.l1k2(x, y, 4)
+        assert (gi.cpu().numpy().view(np.uint64) == oi).all() and (gd.cpu().numpy() == od).all()
+
+
 def test_l1k2_concurrent_callers(po, feature):
-    """The reference's entry points are re-entrant (no globals); this library serialises callers on one mutex
-    around its cached device context (SURVEY 8b 'Threading').  Four threads, different inputs, each result exact."""
+    """The reference's entry points are re-entrant (no globals); here every concurrent caller works on its own
+    context (streams + buffers) taken from a pool (SURVEY 8b 'Threading').  Four threads, different inputs, each result exact."""
     import threading
     rng = np.random.RandomState(77)
     jobs = [(_rand(rng, 2000 + 300 * t, 128, 256), _rand(rng, 700 + 100 * t, 128, 256)) for t in range(4)]
