@@ -11,17 +11,26 @@ src/BruteForceNnL1K2.h:84-145 behind nn_bruteforcel1k2, Spectavi.cpp:284-298):
              N ranks (one process per GPU), query rows replicated, per-rank top-2
              all-gathered over NCCL and merged (K5) every step  -> "strong" scaling
 `value`   : pairs covered / s with inputs resident in HBM (CUDA events, max over ranks)
-`e2e`     : the same through the host-buffer API (nn_bruteforcel1k2 C ABI at N == 1,
-            device.nn_bruteforcel1k2_sharded from pinned host buffers at N > 1),
-            H2D of the descriptors and D2H of (idx, dist) inside the timed region
+`e2e`     : the same through the drop-in call a user makes, feature.nn_bruteforcel1k2 (C ABI
+            nn_bruteforcel1k2) on ordinary PAGEABLE numpy arrays, H2D of the descriptors and D2H
+            of (idx, dist) inside the timed region.  At N > 1 that is the library's own multi-GPU
+            layout (SPECTAVI_GPUS=N: one host thread per GPU, NCCL all-gather of the keys), run
+            by rank 0 while the other ranks wait on a CPU (gloo) barrier; the torchrun layout
+            from pinned buffers is reported beside it in `extras`.
 `roofline`: K1's packed-SAD rate against the VABSDIFF4 issue peak measured in the
-            same run by spv_pipe_peak (the path is ALU-bound)
+            same run by spv_pipe_peak (the path is ALU-bound), and
+            against the nominal 64 per clk per SM
 `cpu_baseline` / --impl reference: the reference's own BruteForceNnL1K2 (oracle/_ref,
             compiled from /root/reference through oracle/eigen_shim; else the C port)
             on all host cores over a bounded slice of query rows against the full
             train set (rows are independent, BruteForceNnL1K2.h:92-93).
+Parity is checked inside the run at every N: the timed GPU result equals the CPU sample bit for
+bit, and `result_hash` (blake2b of the full idx + dist arrays) is the same string at N = 2, 4, 8
+and in the N = 1 line's `extras.c4_n1`.
 """
 import argparse
+import datetime
+import hashlib
 import json
 import os
 import subprocess
@@ -32,6 +41,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 METRIC = "G L1 descriptor-pair comparisons/sec (k=2, 128-D) at 1/2/4/8 B200 vs CPU SSE"
 UNIT = "Gpairs/s"
@@ -50,7 +60,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-peak", action="store_true", help="skip the pipe-peak microbenchmark")
-    ap.add_argument("--no-extras", action="store_true", help="skip the C2 (castle) and C5 (cascade) side measurements")
+    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements (C1, C2, C4 on one GPU, C5, K1f, K8)")
     return ap.parse_args()
 
 
@@ -60,6 +70,11 @@ def workload_of(args, world):
         return name, WORKLOADS[name]
     xr, yr, d = (int(v) for v in name.lower().split("x"))
     return name, (xr, yr, d)
+
+
+def workload_text(wname, xr, yr, dim, world):
+    return "%s: %d train x %d query x %d-D u8, brute-force L1 k=2%s" % (
+        wname, xr, yr, dim, "" if world == 1 else ", train sharded %d-way + NCCL all-gather + top-2 merge" % world)
 
 
 def host_rows(rows, dim, seed, lo=0):
@@ -78,6 +93,30 @@ def host_rows(rows, dim, seed, lo=0):
         out[r:r + n] = rng.integers(0, 256, (blk, dim), dtype=np.uint8)[off:off + n]
         r += n
     return out
+
+
+def sift_like_rows(rows, seed):
+    """SURVEY 8d "S" data: rows sampled with replacement from the 128 descriptor columns of the reference's
+    data/sift-test/sur-ogre.sift (tests/golden/l1k2_sift_surogre.npz) plus +-2 uniform integer noise, clipped.
+    Real SIFT rows are clustered, which is what the CPU's early-exit prune (BruteForceNnL1K2.h:118-121) feeds on."""
+    import numpy as np
+    desc = np.load(os.path.join(ROOT, "tests", "golden", "l1k2_sift_surogre.npz"))["desc"]
+    rng = np.random.Generator(np.random.Philox(key=seed))
+    out = np.empty((rows, 128), np.uint8)
+    for r in range(0, rows, 65536):
+        n = min(65536, rows - r)
+        base = desc[rng.integers(0, desc.shape[0], n)].astype(np.int16)
+        out[r:r + n] = np.clip(base + rng.integers(-2, 3, (n, 128), dtype=np.int16), 0, 255).astype(np.uint8)
+    return out
+
+
+def result_hash(idx, dist):
+    """blake2b-64 of the full (idx uint64 [yrows, 2], dist int32 [yrows, 2]) result."""
+    import numpy as np
+    h = hashlib.blake2b(digest_size=8)
+    h.update(np.ascontiguousarray(idx).view(np.uint8).tobytes())
+    h.update(np.ascontiguousarray(dist).view(np.uint8).tobytes())
+    return h.hexdigest()
 
 
 class ClockSampler:
@@ -140,7 +179,7 @@ def cpu_matcher():
 
 def cpu_sample(x, yfull, budget_s, cores):
     """Time the CPU matcher on a contiguous slice of query rows against the FULL
-    train set, sized to about budget_s seconds; returns (Gpairs/s, rows, seconds)."""
+    train set, sized to about budget_s seconds; returns (kind, Gpairs/s, rows, seconds, result)."""
     import numpy as np
     kind, fn = cpu_matcher()
     probe = min(64 * cores, yfull.shape[0])
@@ -162,8 +201,8 @@ def run_reference(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return 0
-    import numpy as np
-    wname, (xr, yr, dim) = workload_of(args, max(world, args.gpus))
+    ngpu = max(world, args.gpus)
+    wname, (xr, yr, dim) = workload_of(args, ngpu)
     cores = os.cpu_count() or 1
     x = host_rows(xr, dim, 11)
     kind, fn = cpu_matcher()
@@ -183,101 +222,187 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     val = xr * rows * args.steps / dt / 1e9
     sample = "%d of %d query rows x all %d train rows per step (rows independent; pairs covered incl. pruned)" % (rows, yr, xr)
-    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": max(world, args.gpus),
+    extras = {}
+    try:   # the same arm on 1 thread (the reference test's default, spectavi/feature.py:292) and on SIFT-like rows
+        r1 = max(1, rows // cores)
+        t0 = time.perf_counter(); fn(x, y[:r1].copy(), 1); d1 = time.perf_counter() - t0
+        extras["one_thread"] = {"value": xr * r1 / d1 / 1e9, "unit": UNIT, "cores": 1, "sample": "%d query rows x all train rows" % r1}
+        if dim == 128:
+            xs, ys = sift_like_rows(xr, 21), sift_like_rows(rows, 23)
+            t0 = time.perf_counter(); fn(xs, ys, cores); ds = time.perf_counter() - t0
+            extras["sift_like_rows"] = {"value": xr * rows / ds / 1e9, "unit": UNIT, "cores": cores,
+                                        "sample": "%d SIFT-like query rows x %d SIFT-like train rows (SURVEY 8d 'S' data: the prune bites)" % (rows, xr)}
+    except Exception as ex:
+        extras["error"] = repr(ex)[:200]
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": ngpu,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-            "higher_is_better": True, "scaling": "strong" if max(world, args.gpus) > 1 else "weak",
-            "vs_baseline": None, "dtype": "u8", "data": "synthetic uniform u8",
-            "config": {"workload": "%s: %d train x %d query x %d-D u8, brute-force L1 k=2" % (wname, xr, yr, dim),
-                       "sample": sample},
+            "higher_is_better": True, "scaling": "strong" if ngpu > 1 else "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic uniform u8 (Philox, seeded per 64k-row block)",
+            "config": {"workload": workload_text(wname, xr, yr, dim, ngpu),
+                       "l2": "n/a (host cores)", "timing": "perf_counter around the K steps", "sample": sample},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "extras": extras}
     print(json.dumps(line), flush=True)
     return 0
 
 
 # ------------------------------------------------------------------ GPU arm
 def pipe_peak(dev_index):
-    """P_sad4: VABSDIFF4.U8.ACC thread-ops/s measured on this GPU now (pipe_peak.cu)."""
+    """Issue rates measured on this GPU now (pipe_peak.cu): VABSDIFF4.U8.ACC, FP32, FP64 variants."""
     import ctypes as ct
     from spectavi_b200._libspectavi import clib
-    out = (ct.c_double * 64)()
-    names = (ct.c_char_p * 32)()
-    lanes = (ct.c_double * 32)()
+    out = (ct.c_double * 128)()
+    names = (ct.c_char_p * 64)()
+    lanes = (ct.c_double * 64)()
     clib.spv_pipe_peak.restype = ct.c_int
     clib.spv_pipe_peak.argtypes = [ct.c_int, ct.c_int, ct.c_void_p, ct.c_void_p, ct.c_void_p]
     n = clib.spv_pipe_peak(dev_index, 4000, out, names, lanes)
     if n <= 0:
         return None
-    tab = {names[v].decode(): {"ops_per_clk_sm": out[2 * v], "gops": out[2 * v + 1]} for v in range(n)}
-    return tab
+    return {names[v].decode(): {"ops_per_clk_sm": out[2 * v], "gops": out[2 * v + 1]} for v in range(n)}
 
 
-def side_measurements(device):
-    """Not part of the metric: BASELINE.json's other configs measured in the same run, for the record.
-    c2: the castle pair's SIFT rows (tests/golden/castle_c2.npz) through the example's step 2 via the
-    host-buffer API; c5: the cascade-of-hashes matcher at 1M x 1M against brute force (tools/bench_cascade.py)."""
+def guarded(out, key, fn):
+    """A side measurement must never cost the bench line."""
+    try:
+        t0 = time.perf_counter()
+        out[key] = fn()
+        if isinstance(out[key], dict):
+            out[key]["wall_s"] = round(time.perf_counter() - t0, 2)
+    except Exception as ex:
+        out[key] = {"error": repr(ex)[:300]}
+
+
+def extra_c1():
+    """C1 = BASELINE.json configs[0], 4096 x 4096 x 128: the reference's own CPU-runnable case, timed on the GPU
+    (through the C ABI) and on the host with 1 thread (the reference test's default) and all cores."""
+    from spectavi_b200 import feature
+    kind, fn = cpu_matcher()
+    x, y = host_rows(4096, 128, 31), host_rows(4096, 128, 33)
+    feature.nn_bruteforcel1k2(x, y)
+    best = 1e9
+    for _ in range(10):
+        t0 = time.perf_counter(); gi, gd = feature.nn_bruteforcel1k2(x, y); best = min(best, time.perf_counter() - t0)
+    cores = os.cpu_count() or 1
+    t0 = time.perf_counter(); o1 = fn(x, y, 1); t1 = time.perf_counter() - t0
+    t0 = time.perf_counter(); fn(x, y, cores); tn = time.perf_counter() - t0
+    pairs = 4096. * 4096.
+    return {"workload": "c1: 4096 x 4096 x 128 u8", "gpu_e2e_ms": best * 1e3, "gpu_e2e_Gpairs_per_s": pairs / best / 1e9,
+            "cpu_%s_1_thread_ms" % kind: t1 * 1e3, "cpu_1_thread_Gpairs_per_s": pairs / t1 / 1e9,
+            "cpu_%s_%d_threads_ms" % (kind, cores): tn * 1e3, "cpu_all_cores_Gpairs_per_s": pairs / tn / 1e9,
+            "parity_bit_exact": bool((gi == o1[0].reshape(gi.shape)).all() and (gd == o1[1].reshape(gd.shape)).all())}
+
+
+def extra_c2():
+    """The castle pair's SIFT rows (tests/golden/castle_c2.npz) through the example's step 2 via the host-buffer API."""
     import numpy as np
+    from spectavi_b200 import feature
+    g = np.load(os.path.join(ROOT, "tests", "golden", "castle_c2.npz"))
+    s1 = np.hstack([g["k1"], g["d1"].astype("float32")])
+    s2 = np.hstack([g["k2"], g["d2"].astype("float32")])
+    xu = (feature.normalize_to_ubyte_and_multiple_16_dim(s1) + 128).astype("uint8")
+    yu = (feature.normalize_to_ubyte_and_multiple_16_dim(s2) + 128).astype("uint8")
+    feature.nn_bruteforcel1k2(xu, yu)
+    best = 1e9
+    for _ in range(8):
+        t0 = time.perf_counter(); gi, gd = feature.nn_bruteforcel1k2(xu, yu); best = min(best, time.perf_counter() - t0)
+    feature.match_bruteforcel1k2(xu, yu, 1.75)
+    tm = 1e9
+    for _ in range(5):
+        t0 = time.perf_counter(); mx, my = feature.match_bruteforcel1k2(xu, yu, 1.75); tm = min(tm, time.perf_counter() - t0)
+    kind, cfn = cpu_matcher()
+    t0 = time.perf_counter(); cfn(xu, yu, os.cpu_count() or 1); cpu_ms = (time.perf_counter() - t0) * 1e3
+    return {"rows": [int(xu.shape[0]), int(yu.shape[0])], "dim": int(xu.shape[1]),
+            "cpu_%s_ms(all host cores, real SIFT rows: the prune of BruteForceNnL1K2.h:118-121 bites)" % kind: cpu_ms,
+            "nn_bruteforcel1k2_ms_e2e": best * 1e3, "Gpairs_per_s_e2e": xu.shape[0] * yu.shape[0] / best / 1e9,
+            "match_ms_e2e": tm * 1e3, "matches": int(mx.shape[0]),
+            "equals_reference_output": bool((gi == g["idx"].astype(np.uint64)).all() and (gd == g["dist"]).all())}
+
+
+def extra_c3_sift(device, peak_gops):
+    """C3 on SIFT-like ("S") rows: GPU speed is data-independent (no prune), the CPU's is not."""
+    import numpy as np
+    import torch
+    from spectavi_b200 import device as dev
+    xr = yr = 200_000
+    hx, hy = sift_like_rows(xr, 21), sift_like_rows(yr, 23)
+    dx, dy = torch.from_numpy(hx).to(device), torch.from_numpy(hy).to(device)
+    keys = dev.new_keys(yr, device)
+    dev.l1k2_fold(dx, dy, keys, 0)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms = []
+    for _ in range(3):
+        dev.keys_reset(keys)
+        e0.record(); dev.l1k2_fold(dx, dy, keys, 0); e1.record(); torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    gi, gd = dev.keys_finalize(keys)
+    cores = os.cpu_count() or 1
+    kind, gps, rows, secs, (oi, od) = cpu_sample(hx, hy, 6.0, cores)
+    oi, od = oi.reshape(-1, 2), od.reshape(-1, 2)
+    k1 = min(ms)
+    out = {"workload": "c3 on SIFT-like rows (sur-ogre.sift descriptors + noise), 200000 x 200000 x 128", "k1_ms": k1,
+           "Gpairs_per_s": xr * yr / k1 / 1e6, "cpu_%s_Gpairs_per_s" % kind: gps, "cpu_cores": cores,
+           "cpu_sample": "%d query rows, %.1f s" % (rows, secs),
+           "parity_rows_checked": int(oi.shape[0]),
+           "parity_bit_exact": bool((gi[:oi.shape[0]].cpu().numpy().view(np.uint64) == oi).all() and (gd[:oi.shape[0]].cpu().numpy() == od).all())}
+    if peak_gops:
+        out["frac_of_pipe_peak"] = xr * yr * 32. / (k1 * 1e-3) / 1e9 / peak_gops
+    return out
+
+
+def extra_c4_n1(device, peak_gops):
+    """C4 (1M x 1M) on ONE GPU: the like-for-like base of the strong-scaling curve, and the hash every N > 1 line must repeat."""
+    import torch
+    from spectavi_b200 import device as dev
+    xr = yr = 1_000_000
+    dx, dy = torch.from_numpy(host_rows(xr, 128, 11)).to(device), torch.from_numpy(host_rows(yr, 128, 13)).to(device)
+    keys = dev.new_keys(yr, device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms = []
+    for _ in range(2):
+        dev.keys_reset(keys)
+        e0.record(); dev.l1k2_fold(dx, dy, keys, 0); gi, gd = dev.keys_finalize(keys); e1.record(); torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    out = {"workload": workload_text("c4", xr, yr, 128, 1), "ms_per_step": min(ms), "Gpairs_per_s": xr * yr / min(ms) / 1e6,
+           "result_hash": result_hash(gi.cpu().numpy(), gd.cpu().numpy())}
+    if peak_gops:
+        out["frac_of_pipe_peak"] = xr * yr * 32. / (min(ms) * 1e-3) / 1e9 / peak_gops
+    return out
+
+
+def side_measurements(device, peak_gops):
+    """Not part of the metric: BASELINE.json's other configs and the neighbours of the path, measured in the same run."""
     out = {}
-    try:
-        from spectavi_b200 import feature
-        g = np.load(os.path.join(ROOT, "tests", "golden", "castle_c2.npz"))
-        s1 = np.hstack([g["k1"], g["d1"].astype("float32")])
-        s2 = np.hstack([g["k2"], g["d2"].astype("float32")])
-        xu = (feature.normalize_to_ubyte_and_multiple_16_dim(s1) + 128).astype("uint8")
-        yu = (feature.normalize_to_ubyte_and_multiple_16_dim(s2) + 128).astype("uint8")
-        feature.nn_bruteforcel1k2(xu, yu)
-        best = 1e9
-        for _ in range(5):
-            t0 = time.perf_counter(); gi, gd = feature.nn_bruteforcel1k2(xu, yu); best = min(best, time.perf_counter() - t0)
-        t0 = time.perf_counter(); mx, my = feature.match_bruteforcel1k2(xu, yu, 1.75); tm = time.perf_counter() - t0
-        cpu_ms = None
-        try:
-            from oracle import pyoracle as po
-            cfn = po.ref_l1k2 if po.have_ref() else po.l1k2
-            t0 = time.perf_counter(); cfn(xu, yu, os.cpu_count() or 1); cpu_ms = (time.perf_counter() - t0) * 1e3
-        except Exception:
-            pass
-        out["c2_castle"] = {"rows": [int(xu.shape[0]), int(yu.shape[0])], "dim": int(xu.shape[1]),
-                            "cpu_reference_ms(all host cores, real SIFT rows: the prune of BruteForceNnL1K2.h:118-121 bites)": cpu_ms,
-                            "nn_bruteforcel1k2_ms_e2e": best * 1e3, "Gpairs_per_s_e2e": xu.shape[0] * yu.shape[0] / best / 1e9,
-                            "match_ms_e2e": tm * 1e3, "matches": int(mx.shape[0]),
-                            "equals_reference_output": bool((gi == g["idx"].astype(np.uint64)).all() and (gd == g["dist"]).all())}
-    except Exception as ex:                                  # a side measurement must never cost the bench line
-        out["c2_castle"] = {"error": repr(ex)[:200]}
-    try:
-        # the float matcher on the reference test's shape family (test/test_feature.py:67-81), p = 2, k = 2
-        from spectavi_b200 import feature
-        from oracle import pyoracle as po
-        rng = np.random.RandomState(5)
-        res = {}
-        for rows in (1000, 20000):
-            xf = rng.randn(rows, 132).astype("float32")
-            yf = rng.randn(rows, 132).astype("float32")
-            feature.nn_bruteforce(xf, yf, p=2., mu=0., k=2)
-            best = 1e9
-            for _ in range(3):
-                t0 = time.perf_counter(); fi, fd = feature.nn_bruteforce(xf, yf, p=2., mu=0., k=2); best = min(best, time.perf_counter() - t0)
-            ent = {"ms_e2e": best * 1e3, "Gpairs_per_s_e2e": rows * rows / best / 1e9}
-            if rows == 1000:
-                cfn = po.ref_bruteforce if po.have_ref() else po.bruteforce
-                t0 = time.perf_counter(); oi, od = cfn(xf, yf, 2, 2., 0.); ent["cpu_reference_ms(1 thread: BruteForceNn is single-threaded)"] = (time.perf_counter() - t0) * 1e3
-                ent["idx_equal"] = bool((fi == oi).all()); ent["dist_bit_exact"] = bool((fd.view(np.uint32) == od.view(np.uint32)).all())
-            res["%dx%dx132" % (rows, rows)] = ent
-        out["nn_bruteforce_f32_p2"] = res
-    except Exception as ex:
-        out["nn_bruteforce_f32_p2"] = {"error": repr(ex)[:200]}
-    try:
-        sys.path.insert(0, os.path.join(ROOT, "tools"))
+    guarded(out, "c1", extra_c1)
+    guarded(out, "c2_castle", extra_c2)
+    guarded(out, "c3_sift_like", lambda: extra_c3_sift(device, peak_gops))
+    guarded(out, "c4_n1", lambda: extra_c4_n1(device, peak_gops))
+
+    def lp():
+        import bench_lp
+        return bench_lp.run(20000, 3)
+    guarded(out, "k1f_nn_bruteforce_f32", lp)
+
+    def cascade():
         import bench_cascade
-        out["c5_cascade"] = bench_cascade.run(1_000_000, 128, 3, 1000)
-    except Exception as ex:
-        out["c5_cascade"] = {"error": repr(ex)[:200]}
-    try:   # SURVEY.md 8f rank 3: KMedians::find_nearest_neighbours at the castle pair's size
+        return bench_cascade.run(1_000_000, 128, 3, 1000)
+    guarded(out, "c5_cascade", cascade)
+
+    def cascade_castle():
+        import bench_cascade
+        return bench_cascade.run_castle()
+    guarded(out, "c2_castle_cascade", cascade_castle)
+
+    def kmed():
         import bench_kmedians
-        out["kmedians_nn"] = bench_kmedians.run(10000, 132, 5)
-    except Exception as ex:
-        out["kmedians_nn"] = {"error": repr(ex)[:200]}
+        return bench_kmedians.run(10000, 132, 5)
+    guarded(out, "kmedians_nn", kmed)
+
+    def ransac():
+        import bench_ransac
+        return bench_ransac.run()
+    guarded(out, "k8_ransac_scoring", ransac)
     return out
 
 
@@ -292,8 +417,12 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device; this framework has no CPU path (use --impl reference)")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
+        # rank 0 later drives ALL GPUs through the C ABI while the others wait: that wait must not be an NCCL
+        # kernel spinning on their SMs, so it goes through a CPU (gloo) group
+        cpu_group = dist.new_group(backend="gloo", timeout=datetime.timedelta(minutes=60))
     from spectavi_b200 import device as dev
     from spectavi_b200 import feature
 
@@ -352,54 +481,84 @@ def run_b200(args):
     value = pairs * args.steps / (step_ms * 1e-3) / 1e9
     result_idx, result_dist = idx, dd
 
-    # ---- e2e: host buffers in, host results out, copies inside the timed region
-    e2e = None
-    if not args.no_e2e:
-        esteps = args.steps
-        h2d = (xn + yr) * dim
-        d2h = yr * 2 * (8 + 4)
-        if world == 1:
-            # ordinary pageable numpy arrays, as a user's are (NOT views of the pinned tensors above)
-            nx, ny = np.empty(hx.shape, np.uint8), np.empty(hy.shape, np.uint8)
-            nx[...] = hx.numpy(); ny[...] = hy.numpy()
-            for _ in range(2):
-                feature.nn_bruteforcel1k2(nx, ny)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            for _ in range(esteps):
-                ei, ed = feature.nn_bruteforcel1k2(nx, ny)
-            e_s = time.perf_counter() - t0
-        else:
-            def estep():
-                ex = hx.to(device, non_blocking=True)
-                ey = hy.to(device, non_blocking=True)
-                gi, gd = dev.nn_bruteforcel1k2_sharded(ex, ey, x0)
-                if rank == 0:
-                    return gi.cpu(), gd.cpu()
-                return None
-            for _ in range(2):
-                estep()
-            barrier()
-            t0 = time.perf_counter()
-            for _ in range(esteps):
-                estep()
-            barrier()
-            e_s = time.perf_counter() - t0
-            tt = torch.tensor([e_s], dtype=torch.float64, device=device)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            e_s = float(tt[0])
-        e2e = {"value": pairs * esteps / e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h if rank == 0 else 0), "ms_per_step": e_s / esteps * 1e3,
-               "api": "feature.nn_bruteforcel1k2 (C ABI nn_bruteforcel1k2, host numpy buffers)" if world == 1 else
-                      "device.nn_bruteforcel1k2_sharded from pinned host buffers, result to host on rank 0"}
+    # ---- torchrun layout end to end (N > 1): pinned shard + query rows up, sharded match, result to rank 0's host
+    torchrun_e2e = None
+    if world > 1 and not args.no_e2e:
+        def estep():
+            ex = hx.to(device, non_blocking=True)
+            ey = hy.to(device, non_blocking=True)
+            gi, gd = dev.nn_bruteforcel1k2_sharded(ex, ey, x0)
+            if rank == 0:
+                return gi.cpu(), gd.cpu()
+            return None
+        for _ in range(2):
+            estep()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            estep()
+        barrier()
+        e_s = time.perf_counter() - t0
+        tt = torch.tensor([e_s], dtype=torch.float64, device=device)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e_s = float(tt[0])
+        torchrun_e2e = {"value": pairs * args.steps / e_s / 1e9, "unit": UNIT, "ms_per_step": e_s / args.steps * 1e3,
+                        "api": "device.nn_bruteforcel1k2_sharded from pinned host buffers (one process per GPU), result to host on rank 0"}
+        barrier()
+
+    c5_sharded = None
+    if world > 1 and not args.no_extras:      # C5 at N GPUs (BASELINE.json configs[4]); every rank takes part
+        try:
+            import bench_cascade
+            c5_sharded = bench_cascade.run_sharded(device, world, rank)
+        except Exception as ex:
+            c5_sharded = {"error": repr(ex)[:300]}
+        barrier()
 
     if rank != 0:
-        if world > 1:
-            dist.barrier()
-            dist.destroy_process_group()
+        dist.barrier(group=cpu_group)          # CPU-side wait: rank 0 is about to use this GPU through the C ABI
+        dist.destroy_process_group()
         return 0
 
-    # ---- rank 0: roofline, cpu baseline, the JSON line
+    # ---- rank 0 from here on.  e2e: the drop-in call on pageable numpy arrays
+    e2e = None
+    c_abi = {}
+    if not args.no_e2e:
+        xfull = np.empty((xr, dim), np.uint8)       # ordinary pageable arrays, as a user's are
+        yfull = np.empty((yr, dim), np.uint8)
+        if world == 1:
+            xfull[...] = hx.numpy()
+        else:
+            xfull[...] = host_rows(xr, dim, 11)
+            os.environ["SPECTAVI_GPUS"] = str(world)   # read once, at the library's first host-buffer call
+        yfull[...] = hy.numpy()
+        try:
+            for _ in range(2):
+                feature.nn_bruteforcel1k2(xfull, yfull)
+            torch.cuda.synchronize()
+            esteps = args.steps if world == 1 else max(3, min(args.steps, 5))
+            la = dev.launch_count()
+            t0 = time.perf_counter()
+            for _ in range(esteps):
+                ei, ed = feature.nn_bruteforcel1k2(xfull, yfull)
+            e_s = time.perf_counter() - t0
+            lb = dev.launch_count()
+            e2e = {"value": pairs * esteps / e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": int((xr + yr * world) * dim),
+                   "d2h_bytes_per_step": int(yr * 2 * (8 + 4)), "ms_per_step": e_s / esteps * 1e3, "steps": esteps,
+                   "kernel_launches_per_step": int((lb - la) // esteps),
+                   "api": "feature.nn_bruteforcel1k2 (C ABI nn_bruteforcel1k2) on pageable numpy arrays" +
+                          ("" if world == 1 else "; SPECTAVI_GPUS=%d: one process, one host thread per GPU, NCCL all-gather of the keys" % world)}
+            gi_t = result_idx.cpu().numpy().view(np.uint64)
+            c_abi = {"equals_device_resident_result": bool((ei == gi_t).all() and (ed == result_dist.cpu().numpy()).all()),
+                     "result_hash": result_hash(ei, ed)}
+            e2e.update(c_abi)
+        except Exception as ex:
+            e2e = None
+            c_abi = {"error": repr(ex)[:300]}
+        if e2e is None and torchrun_e2e is not None:   # keep an end-to-end figure if the C-ABI leg failed
+            e2e = dict(torchrun_e2e, h2d_bytes_per_step=int((xn + yr) * dim), d2h_bytes_per_step=int(yr * 24))
+
+    # ---- roofline
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -413,14 +572,20 @@ def run_b200(args):
             "hbm_floor": {"bytes": int((xn + yr) * dim + yr * 16), "achieved_GBps": ((xn + yr) * dim + yr * 16) / (k1_ms * 1e-3) / 1e9,
                           "peak_GBps": peaks.get("hbm_gbs", 6650.0),
                           "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"}}
+    sms = torch.cuda.get_device_properties(local).multi_processor_count
+    mhz = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
+    nominal = 64.0 * sms * mhz * 1e6 / 1e9
+    roof["peak_nominal"] = nominal
+    roof["frac_nominal"] = achieved / nominal
+    roof["peak_nominal_source"] = "64 VABSDIFF4 per clk per SM (half-rate ALU pipe) x %d SMs x %.0f MHz" % (sms, mhz)
+    peak_gops = None
     if not args.no_peak:
         tab = pipe_peak(local)
         if tab:
             sad = [v for k, v in tab.items() if k.startswith("sad4_acc(")][0]
+            peak_gops = sad["gops"]
             roof["peak"] = sad["gops"]
             roof["frac"] = achieved / sad["gops"]
-            sms = torch.cuda.get_device_properties(local).multi_processor_count
-            mhz = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
             roof["peak_source"] = ("spv_pipe_peak in this run (pipe_peak.cu): VABSDIFF4.U8.ACC issues %.0f G thread-ops/s on an idle "
                                    "GPU (burst, CUDA events) = %.1f per clk per SM at %d SMs x %.0f MHz (nominal 64: half-rate ALU pipe)"
                                    % (sad["gops"], sad["gops"] * 1e3 / (sms * mhz), sms, mhz))
@@ -433,39 +598,55 @@ def run_b200(args):
     except Exception:
         pass
 
+    # ---- CPU baseline on a bounded sample; its results double as the parity check of the timed GPU output, at every N
     cpu = None
+    parity = {"result_hash": result_hash(result_idx.cpu().numpy().view(np.uint64), result_dist.cpu().numpy())}
     if not args.no_cpu:
         cores = os.cpu_count() or 1
-        xfull = hx.numpy() if world == 1 else host_rows(xr, dim, 11)
-        kind, gps, rows, secs, (oi, od) = cpu_sample(xfull, hy.numpy(), args.cpu_seconds, cores)
+        xall = hx.numpy() if world == 1 else host_rows(xr, dim, 11)
+        kind, gps, rows, secs, (oi, od) = cpu_sample(xall, hy.numpy(), args.cpu_seconds, cores)
         cpu = {"value": gps, "unit": UNIT, "cores": cores, "kind": kind,
                "sample": "first %d of %d query rows x all %d train rows, %.1f s wall, extrapolated by rows (rows independent)" % (rows, yr, xr, secs)}
-        if world == 1:
-            # the CPU leg's results double as a parity check of the timed GPU output: every sampled query row
-            oi, od = oi.reshape(-1, 2), od.reshape(-1, 2)
-            gi = result_idx[:oi.shape[0]].cpu().numpy().view(np.uint64)
-            gd = result_dist[:oi.shape[0]].cpu().numpy()
-            cpu["parity_rows_checked"] = int(oi.shape[0])
-            cpu["parity_bit_exact"] = bool((gi == oi).all() and (gd == od).all())
+        oi, od = oi.reshape(-1, 2), od.reshape(-1, 2)
+        gi = result_idx[:oi.shape[0]].cpu().numpy().view(np.uint64)
+        gd = result_dist[:oi.shape[0]].cpu().numpy()
+        parity["parity_rows_checked"] = int(oi.shape[0])
+        parity["parity_bit_exact"] = bool((gi == oi).all() and (gd == od).all())
+        cpu.update(parity)
+        try:   # 1 thread: the reference test's default (spectavi/feature.py:292)
+            kindf, fn = cpu_matcher()
+            r1 = max(16, rows // cores)
+            t0 = time.perf_counter(); fn(xall, np.ascontiguousarray(hy.numpy()[:r1]), 1); d1 = time.perf_counter() - t0
+            cpu["one_thread"] = {"value": xr * r1 / d1 / 1e9, "unit": UNIT, "cores": 1, "sample": "%d query rows x all train rows" % r1}
+        except Exception as ex:
+            cpu["one_thread"] = {"error": repr(ex)[:200]}
 
-    extras = None
-    if world == 1 and not args.no_extras:
-        extras = side_measurements(device)
+    extras = {}
+    if not args.no_extras:
+        if world == 1:
+            extras = side_measurements(device, peak_gops)
+        else:
+            if torchrun_e2e is not None:
+                extras["torchrun_layout_e2e"] = torchrun_e2e
+            extras["c_abi_mgpu"] = dict(c_abi, note="timed as the e2e figure of this line")
+            if c5_sharded is not None:
+                extras["c5_cascade_sharded"] = c5_sharded
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3) if args.warmup else 0, "ms_per_step": step_ms / args.steps,
             "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic uniform u8 (Philox, seeded per 64k-row block)",
-            "config": {"workload": "%s: %d train x %d query x %d-D u8, brute-force L1 k=2%s" % (
-                           wname, xr, yr, dim, "" if world == 1 else ", train sharded %d-way + NCCL all-gather + top-2 merge" % world),
+            "config": {"workload": workload_text(wname, xr, yr, dim, world),
                        "l2": "L2 flushed between timed steps by a %d MiB fill outside the event pair" % (L2_FLUSH_BYTES >> 20),
-                       "timing": "CUDA events per step on the launching stream, summed, max over ranks"},
+                       "timing": "CUDA events per step on the launching stream, summed, max over ranks",
+                       "sample": "full workload every step"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(l1 - l0), "roofline": roof, "cpu_baseline": cpu}
+    line.update(parity)
     if extras:
         line["extras"] = extras
     print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=cpu_group)
         dist.destroy_process_group()
     return 0
 

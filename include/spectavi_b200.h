@@ -17,6 +17,7 @@
 #ifndef SPECTAVI_B200_H
 #define SPECTAVI_B200_H
 
+#include <stdbool.h>
 #include <stddef.h>
 #include <stdint.h>
 
@@ -120,6 +121,35 @@ void spv_kmedians_find_nearest_neighbours(const float *x, const float *y, int xr
                                           const float *medians_y, const int32_t *labels_y, int nmy, int c, int k,
                                           NdArray *outidx, NdArray *outdist);
 
+/* ---- Part 1d: the step AFTER the matcher: RANSAC hypothesis scoring.
+ * The reference's ransac_fitter (src/Spectavi.cpp:70-88 -> RansacFitter::fit_essential, src/RansacFitter.h:154-277)
+ * draws 7 matches per try from std::random_device, solves the seven-point system (out of scope here) and scores
+ * every resulting fundamental matrix with process_fundamental_matrix (RansacFitter.h:42-98): SVD gate, the four
+ * cameras of Essential2Cameras (src/Camera.h:32-59), a DLT triangulation (src/DltTriangulator.h:36-92) of EVERY
+ * match against every camera, inliers = reprojection error <= allowed and in front of both cameras.  These entry
+ * points take the candidate matrices (F: nF x 9 row-major, from any seven-point solver) and do the scoring on the
+ * GPU, all hypotheses x 4 cameras x all matches in one launch.  x0, x1: npt x 3 homogeneous normalised points
+ * (npt >= 10, as the reference's constructor demands).
+ *
+ * spv_ransac_process_fundamental_matrices: per hypothesis what process_fundamental_matrix returns -- ok (int32,
+ * its bool), ninlier (int32), cameras (float64 nF x 12: the winning 3 x 4 camera, row-major) and, when masks is not
+ * NULL, the winner's inliers as bit masks (uint32 nF x ceil(npt / 32), bit = match & 31).
+ * spv_ransac_fit_hypotheses: ransac_fitter's outputs (Spectavi.cpp:81-87) for the hypothesis list taken in order
+ * with fit_essential's bookkeeping: the first hypothesis whose inlier percent exceeds required_percent_inliers wins
+ * (success = true); otherwise, with find_best_even_in_failure, the best one seen.  essential = the winning F,
+ * camera 3 x 4, inlier_idx int32 (ascending).
+ * Arithmetic: Eigen's JacobiSVD is restated (two-sided Jacobi); results equal the reference's code
+ * compiled against that restatement bit for bit, and a LAPACK-based check up to matches within 1e-9 of the threshold. */
+void spv_ransac_process_fundamental_matrices(const double *x0, const double *x1, int npt,
+                                             double required_percent_inliers, double reprojection_error_allowed,
+                                             int find_best_even_in_failure, double singular_value_ratio_allowed,
+                                             const double *F, int nF, NdArray *ok, NdArray *ninlier, NdArray *cameras,
+                                             NdArray *masks);
+void spv_ransac_fit_hypotheses(const double *x0, const double *x1, int npt, double required_percent_inliers,
+                               double reprojection_error_allowed, int find_best_even_in_failure,
+                               double singular_value_ratio_allowed, const double *F, int nF, bool *success,
+                               NdArray *essential, NdArray *camera, double *inlier_percent, NdArray *inlier_idx);
+
 /* ============================ Part 2: device-resident API (device pointers)
  * Results live in a KEY buffer: uint64 keys[2][yrows], key = dist << 32 | idx,
  * all-ones = none; unsigned order of keys == the reference's (dist, idx) rule. */
@@ -182,6 +212,15 @@ int spv_hash_codes_device(const uint8_t *drows, int rows, int dim, int m, int n,
  * (CascadingHashNn.h:86-100) over std::mt19937(seed); quantize: multiples of 1/32 */
 void spv_cascade_dictionary(unsigned seed, int dim, int m, int n, int quantize, float *out);
 unsigned spv_cascade_seed(void);
+
+/* K8: RansacFitter::process_fundamental_matrix (src/RansacFitter.h:42-98) for nF fundamental matrices on device
+ * pointers: dF [nF][9], dx0 / dx1 [npt][3] float64.  Outputs [nF]: dok, dcount (int32), dcams [nF][12] float64,
+ * dmasks (nullable) [nF][ceil(npt / 32)] uint32.  dws: spv_ransac_ws_bytes(nF, npt) of scratch. */
+size_t spv_ransac_ws_bytes(int nF, int npt);
+int spv_ransac_score_device(const double *dF, int nF, const double *dx0, const double *dx1, int npt,
+                            double required_percent_inliers, double reprojection_error_allowed,
+                            int find_best_even_in_failure, double singular_value_ratio_allowed, int32_t *dok,
+                            int32_t *dcount, double *dcams, uint32_t *dmasks, void *dws, size_t ws_bytes, void *stream);
 
 /* number of kernels this library has launched since it was loaded */
 uint64_t spv_launch_count(void);

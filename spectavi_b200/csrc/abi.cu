@@ -14,6 +14,7 @@
 #include <cstdarg>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 namespace spv {
 
@@ -162,6 +163,20 @@ int spv_hash_codes_device(const uint8_t* drows, int rows, int dim, int m, int n,
   return 0;
 }
 
+size_t spv_ransac_ws_bytes(int nF, int npt) { return ransac_ws_bytes(nF, npt); }
+
+int spv_ransac_score_device(const double* dF, int nF, const double* dx0, const double* dx1, int npt,
+                            double required_percent_inliers, double reprojection_error_allowed, int find_best_even_in_failure,
+                            double singular_value_ratio_allowed, int32_t* dok, int32_t* dcount, double* dcams,
+                            uint32_t* dmasks, void* dws, size_t ws_bytes, void* stream) {
+  if (nF < 0 || npt < 1) return fail("bad shape: %d hypotheses, %d matches", nF, npt);
+  if (ws_bytes < ransac_ws_bytes(nF, npt)) return fail("workspace too small");
+  CU_OR_FAIL(ransac_score(dF, nF, dx0, dx1, npt, required_percent_inliers, reprojection_error_allowed,
+                          find_best_even_in_failure != 0, singular_value_ratio_allowed, dok, dcount, dcams, dmasks, dws,
+                          ws_bytes, (cudaStream_t)stream));
+  return 0;
+}
+
 void spv_cascade_dictionary(unsigned seed, int dim, int m, int n, int quantize, float* out) {
   cascade_dictionary(seed, dim, m, n, quantize != 0, out);
 }
@@ -275,6 +290,84 @@ void spv_kmedians_find_nearest_neighbours(const float* x, const float* y, int xr
   HostCall hc(fn);
   hc.kmedians_nn(x, y, xrows, yrows, dim, medians_x, labels_x, nmx, medians_y, labels_y, nmy, c, k,
                  reinterpret_cast<uint64_t*>(outidx->m_data), reinterpret_cast<float*>(outdist->m_data));
+}
+
+// ---- Part 1d: the step after the matcher: RANSAC hypothesis scoring
+static void ransac_check(const char* fn, int npt, int nF) {
+  // RansacFitter's constructor throws on these (RansacFitter.h:139-148)
+  if (npt < 10) die(fn, "Supplied less than 10 point matches, unsupported.");
+  if (nF < 0) die(fn, "negative hypothesis count");
+}
+
+void spv_ransac_process_fundamental_matrices(const double* x0, const double* x1, int npt, double required_percent_inliers,
+                                             double reprojection_error_allowed, int find_best_even_in_failure,
+                                             double singular_value_ratio_allowed, const double* F, int nF, NdArray* ok,
+                                             NdArray* ninlier, NdArray* cameras, NdArray* masks) {
+  const char* fn = "spv_ransac_process_fundamental_matrices";
+  ransac_check(fn, npt, nF);
+  out_alloc(ok, (uint64_t)nF, 1);
+  out_alloc(ninlier, (uint64_t)nF, 1);
+  out_alloc(cameras, (uint64_t)nF, 12);
+  if (masks) out_alloc(masks, (uint64_t)nF, (uint64_t)((npt + 31) / 32));
+  if (nF == 0) return;
+  HostCall hc(fn);
+  hc.ransac(x0, x1, npt, required_percent_inliers, reprojection_error_allowed, find_best_even_in_failure != 0,
+            singular_value_ratio_allowed, F, nF, false, reinterpret_cast<int32_t*>(ok->m_data),
+            reinterpret_cast<int32_t*>(ninlier->m_data), reinterpret_cast<double*>(cameras->m_data),
+            masks ? reinterpret_cast<uint32_t*>(masks->m_data) : nullptr);
+}
+
+void spv_ransac_fit_hypotheses(const double* x0, const double* x1, int npt, double required_percent_inliers,
+                               double reprojection_error_allowed, int find_best_even_in_failure,
+                               double singular_value_ratio_allowed, const double* F, int nF, bool* success,
+                               NdArray* essential, NdArray* camera, double* inlier_percent, NdArray* inlier_idx) {
+  const char* fn = "spv_ransac_fit_hypotheses";
+  ransac_check(fn, npt, nF);
+  const int W = (npt + 31) / 32;
+  std::vector<int32_t> ok((size_t)nF), cnt((size_t)nF);
+  std::vector<double> cams((size_t)nF * 12);
+  std::vector<uint32_t> masks((size_t)nF * W);
+  int scored = 0;
+  if (nF > 0) {
+    HostCall hc(fn);
+    scored = hc.ransac(x0, x1, npt, required_percent_inliers, reprojection_error_allowed, find_best_even_in_failure != 0,
+                       singular_value_ratio_allowed, F, nF, true, ok.data(), cnt.data(), cams.data(), masks.data());
+  }
+  // fit_essential's bookkeeping (RansacFitter.h:166-199), the tries taken in order: a scored hypothesis replaces the
+  // best so far when (percent > required || find_best) and percent > best percent; the first one above `required`
+  // ends the search.
+  bool succ = false;
+  double best_pct = 0;
+  int best = -1;
+  for (int i = 0; i < scored && !succ; ++i) {
+    if (!ok[i]) continue;
+    const double pct = (double)cnt[i] / (double)npt;
+    if ((pct > required_percent_inliers || find_best_even_in_failure) && best_pct < pct) {
+      succ = pct > required_percent_inliers;
+      best_pct = pct;
+      best = i;
+    }
+  }
+  *success = succ;
+  *inlier_percent = best_pct;
+  // ndarray_copy_matrix of the members (Spectavi.cpp:82-87): never-assigned members are 0 x 0, the default camera is I(3,4)
+  if (best >= 0) {
+    out_alloc(essential, 3, 3);
+    memcpy(essential->m_data, F + (size_t)best * 9, 9 * 8);
+    out_alloc(camera, 3, 4);
+    memcpy(camera->m_data, cams.data() + (size_t)best * 12, 12 * 8);
+    out_alloc(inlier_idx, (uint64_t)cnt[best], 1);
+    int32_t* o = reinterpret_cast<int32_t*>(inlier_idx->m_data);
+    int k = 0;
+    for (int ix = 0; ix < npt; ++ix)
+      if ((masks[(size_t)best * W + (ix >> 5)] >> (ix & 31)) & 1u) o[k++] = ix;
+  } else {
+    out_alloc(essential, 0, 0);
+    out_alloc(camera, 3, 4);
+    double* c = reinterpret_cast<double*>(camera->m_data);
+    for (int i = 0; i < 12; ++i) c[i] = (i % 5 == 0) ? 1.0 : 0.0;
+    out_alloc(inlier_idx, 0, 0);
+  }
 }
 
 void nn_cascading_hash(const float* x, const float* y, int xrows, int yrows, int dim, int k, int hash_bit_rate,

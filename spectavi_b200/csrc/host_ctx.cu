@@ -462,6 +462,54 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
   sync_all(fn_, c);
 }
 
+int HostCall::ransac(const double* x0, const double* x1, int npt, double required, double err_allowed, bool find_best,
+                     double sv_ratio, const double* F, int nF, bool stop_at_success, int32_t* ok, int32_t* ninlier,
+                     double* cams, uint32_t* masks) {
+  // single GPU: hypotheses are independent, so a multi-GPU split would be trivial, but the matcher's callers
+  // (example/ex01:134-152) stop at the first success, which a few thousand hypotheses usually reach
+  Gpu& D = ctx_->gpus[0];
+  CU(fn_, cudaSetDevice(D.dev));
+  const int W = (npt + 31) / 32;
+  const int B = nF < 16384 ? nF : 16384;                       // hypotheses per launch
+  const size_t pb = (size_t)npt * 3 * 8, wsb = ransac_ws_bytes(B, npt);
+  CU(fn_, D.x.ensure(pb));
+  CU(fn_, D.y.ensure(pb));
+  CU(fn_, D.xf.ensure((size_t)B * 9 * 8));
+  CU(fn_, D.ws.ensure(wsb));
+  CU(fn_, D.oidx.ensure((size_t)B * 8));                       // ok, ninlier
+  CU(fn_, D.odist.ensure((size_t)B * 12 * 8));
+  if (masks) CU(fn_, D.gather.ensure((size_t)B * W * 4));
+  CU(fn_, cudaMemcpyAsync(D.x.p, x0, pb, cudaMemcpyHostToDevice, D.stream));
+  CU(fn_, cudaMemcpyAsync(D.y.p, x1, pb, cudaMemcpyHostToDevice, D.stream));
+  int done = 0;
+  while (done < nF) {
+    const int nb = nF - done < B ? nF - done : B;
+    int32_t* dok = (int32_t*)D.oidx.p;
+    int32_t* dcnt = dok + B;
+    CU(fn_, cudaMemcpyAsync(D.xf.p, F + (size_t)done * 9, (size_t)nb * 9 * 8, cudaMemcpyHostToDevice, D.stream));
+    CU(fn_, ransac_score((const double*)D.xf.p, nb, (const double*)D.x.p, (const double*)D.y.p, npt, required, err_allowed,
+                         find_best, sv_ratio, dok, dcnt, (double*)D.odist.p, masks ? (uint32_t*)D.gather.p : nullptr, D.ws.p,
+                         D.ws.cap, D.stream));
+    CU(fn_, cudaMemcpyAsync(ok + done, dok, (size_t)nb * 4, cudaMemcpyDeviceToHost, D.stream));
+    CU(fn_, cudaMemcpyAsync(ninlier + done, dcnt, (size_t)nb * 4, cudaMemcpyDeviceToHost, D.stream));
+    CU(fn_, cudaMemcpyAsync(cams + (size_t)done * 12, D.odist.p, (size_t)nb * 12 * 8, cudaMemcpyDeviceToHost, D.stream));
+    if (masks) CU(fn_, cudaMemcpyAsync(masks + (size_t)done * W, D.gather.p, (size_t)nb * W * 4, cudaMemcpyDeviceToHost, D.stream));
+    CU(fn_, cudaStreamSynchronize(D.stream));
+    done += nb;
+    if (stop_at_success) {
+      bool hit = false;
+      for (int i = done - nb; i < done && !hit; ++i) hit = ok[i] && (double)ninlier[i] / (double)npt > required;
+      if (hit) break;
+    }
+  }
+  for (int i = done; i < nF; ++i) {
+    ok[i] = 0; ninlier[i] = 0;
+    for (int k = 0; k < 12; ++k) cams[(size_t)i * 12 + k] = 0.0;
+    if (masks) for (int w = 0; w < W; ++w) masks[(size_t)i * W + w] = 0u;
+  }
+  return done;
+}
+
 void HostCall::normalize(const float* x, int rows, int dim, float* out) {
   Gpu& D = ctx_->gpus[0];
   CU(fn_, cudaSetDevice(D.dev));

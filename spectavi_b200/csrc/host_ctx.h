@@ -60,6 +60,15 @@ class HostCall {
   void cascade(const float* x, const float* y, int xrows, int yrows, int dim, int kcols, int m, int n, int g,
                uint64_t* idx, float* dist, const MatchSink* ms = nullptr);
 
+  // K8: RansacFitter::process_fundamental_matrix for nF fundamental matrices (host in / host out).  ok / ninlier
+  // [nF], cams [nF][12], masks (nullable) [nF][ceil(npt / 32)] words.  stop_at_success: hypotheses are scored in
+  // batches and scoring stops behind the first batch that holds a hypothesis with percent > required, as
+  // fit_essential's tries do (RansacFitter.h:189-191); entries of later batches are then left ok = 0.
+  // Returns the number of hypotheses actually scored.
+  int ransac(const double* x0, const double* x1, int npt, double required, double err_allowed, bool find_best,
+             double sv_ratio, const double* F, int nF, bool stop_at_success, int32_t* ok, int32_t* ninlier, double* cams,
+             uint32_t* masks);
+
   // the quantiser (feature.py:384-407): rows x dim float32 in, rows x ceil16(dim) float32 out
   void normalize(const float* x, int rows, int dim, float* out);
 

@@ -42,6 +42,11 @@ enum Variant {
   V_FADD,              // FADD acc, acc, a
   V_FSUB_ABSADD,       // FADD d, a, -b ; FADD acc, acc, |d|   (K1f's p = 1 pair-column, lp_topk.cu)
   V_FSUB_FMUL_FADD,    // FADD d ; FMUL d*d ; FADD acc         (K1f's p = 2 pair-column, no FMA contraction)
+  V_FADD2,             // add.rn.f32x2 (SASS FADD2): two IEEE-rn float adds per instruction
+  V_F2_SUB_ABSADD,     // FADD2 d, a, -b ; FADD2 acc, acc, |d|  (two p = 1 pair-columns per instruction pair)
+  V_F2_SUB_MUL_ADD,    // FADD2 ; FMUL2 ; FADD2                 (two p = 2 pair-columns per instruction triple)
+  V_DFMA,              // fma.rn.f64
+  V_DMUL_DADD,         // mul.rn.f64 ; add.rn.f64               (K8's arithmetic: no contraction, ransac.cu)
   V_COUNT
 };
 
@@ -160,6 +165,53 @@ __global__ void __launch_bounds__(256, 2) peak_kernel(const uint32_t* __restrict
         asm volatile("mul.rn.f32 %0, %0, %0;" : "+f"(d));
         asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(*reinterpret_cast<float*>(&acc[i])) : "f"(d));
       }
+    } else if (V == V_FADD2) {
+#pragma unroll
+      for (int i = 0; i < NACC; i += 2) {
+        unsigned long long c = ((unsigned long long)acc[i + 1] << 32) | acc[i], x = ((unsigned long long)a[(i + 1) & 7] << 32) | a[i & 7];
+        asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(c) : "l"(x));
+        acc[i] = (uint32_t)c; acc[i + 1] = (uint32_t)(c >> 32);
+      }
+    } else if (V == V_F2_SUB_ABSADD) {
+#pragma unroll
+      for (int i = 0; i < NACC; i += 2) {
+        const int o = (i + 16) & (NACC - 1);
+        float2 x = make_float2(__uint_as_float(a[i & 7]), __uint_as_float(a[(i + 1) & 7]));
+        float2 y = make_float2(__uint_as_float(acc[o]), __uint_as_float(acc[o + 1]));   // another chain's accumulators: nothing hoists
+        float2 c = make_float2(__uint_as_float(acc[i]), __uint_as_float(acc[i + 1]));
+        float2 d = __fadd2_rn(x, make_float2(-y.x, -y.y));
+        c = __fadd2_rn(c, make_float2(fabsf(d.x), fabsf(d.y)));
+        acc[i] = __float_as_uint(c.x); acc[i + 1] = __float_as_uint(c.y);
+      }
+    } else if (V == V_F2_SUB_MUL_ADD) {
+#pragma unroll
+      for (int i = 0; i < NACC; i += 2) {
+        const int o = (i + 16) & (NACC - 1);
+        float2 x = make_float2(__uint_as_float(a[i & 7]), __uint_as_float(a[(i + 1) & 7]));
+        float2 y = make_float2(__uint_as_float(acc[o]), __uint_as_float(acc[o + 1]));
+        float2 c = make_float2(__uint_as_float(acc[i]), __uint_as_float(acc[i + 1]));
+        float2 d = __fadd2_rn(x, make_float2(-y.x, -y.y));
+        d = __fmul2_rn(d, d);
+        c = __fadd2_rn(c, d);
+        acc[i] = __float_as_uint(c.x); acc[i + 1] = __float_as_uint(c.y);
+      }
+    } else if (V == V_DFMA) {
+#pragma unroll
+      for (int i = 0; i < NACC; i += 2) {
+        double c = __hiloint2double((int)acc[i + 1], (int)acc[i]);
+        const double x = __hiloint2double((int)(a[i & 7] & 0x000FFFFFu) | 0x3FF00000, (int)a[(i + 1) & 7]);
+        asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(c) : "d"(x));
+        acc[i] = (uint32_t)__double2loint(c); acc[i + 1] = (uint32_t)__double2hiint(c);
+      }
+    } else if (V == V_DMUL_DADD) {
+#pragma unroll
+      for (int i = 0; i < NACC; i += 2) {
+        double c = __hiloint2double((int)acc[i + 1], (int)acc[i]);
+        const double x = __hiloint2double((int)(a[i & 7] & 0x000FFFFFu) | 0x3FF00000, (int)a[(i + 1) & 7]);
+        asm volatile("mul.rn.f64 %0, %0, %1;" : "+d"(c) : "d"(x));
+        asm volatile("add.rn.f64 %0, %0, %1;" : "+d"(c) : "d"(x));
+        acc[i] = (uint32_t)__double2loint(c); acc[i + 1] = (uint32_t)__double2hiint(c);
+      }
     }
   }
   long long t1 = clock64();
@@ -186,6 +238,11 @@ const Desc kDesc[V_COUNT] = {
   {"FADD", NACC, 0},
   {"f32 sub + |.|add (2 FADD)", NACC, 1},          // op = one pair-column of K1f at p = 1
   {"f32 sub + mul + add (FADD FMUL FADD)", NACC, 1},
+  {"FADD2 (add.rn.f32x2)", NACC / 2, 2},                        // op = one instruction = two float adds
+  {"f32x2 sub + |.|add (2 FADD2 per 2)", NACC, 1},               // op = one p = 1 pair-column
+  {"f32x2 sub + mul + add (FADD2 FMUL2 FADD2 per 2)", NACC, 1},  // op = one p = 2 pair-column
+  {"DFMA", NACC / 2, 1},
+  {"f64 mul + add (DMUL DADD)", NACC / 2, 1},                    // op = one multiply-add pair, not contracted
 };
 
 template <int V>
@@ -237,7 +294,8 @@ extern "C" int spv_pipe_peak(int device, int iters, double* out, const char** na
 #define RUN(V) if (!rc) rc = run_variant<V>(sms, cps, iters, din, dout, dcyc, &out[V * 2], &out[V * 2 + 1]);
   RUN(V_SAD4_ACC) RUN(V_SAD4_DP4A) RUN(V_HALF2_ABS) RUN(V_IADD3) RUN(V_LOP3) RUN(V_IMAD) RUN(V_FFMA)
   RUN(V_VIMNMX) RUN(V_VIMNMX3) RUN(V_DP4A) RUN(V_SAD4_ACC_IMAD) RUN(V_SAD4_ACC_IMAD11) RUN(V_SAD4_TILE) RUN(V_SAD_SCALAR)
-  RUN(V_FADD) RUN(V_FSUB_ABSADD) RUN(V_FSUB_FMUL_FADD)
+  RUN(V_FADD) RUN(V_FSUB_ABSADD) RUN(V_FSUB_FMUL_FADD) RUN(V_FADD2) RUN(V_F2_SUB_ABSADD) RUN(V_F2_SUB_MUL_ADD)
+  RUN(V_DFMA) RUN(V_DMUL_DADD)
 #undef RUN
   for (int v = 0; v < V_COUNT; ++v) { if (names) names[v] = kDesc[v].name; if (lanes_per_op) lanes_per_op[v] = kDesc[v].lanes_per_op; }
   cudaFree(din); cudaFree(dout); cudaFree(dcyc);

@@ -87,6 +87,15 @@ size_t normalize_ws_bytes(int dim);
 int normalize_new_dim(int dim);
 cudaError_t normalize_rows(const float* dx, int rows, int dim, float* dout_f32, uint8_t* dout_u8, void* ws, size_t ws_bytes,
                            cudaStream_t stream);
+// ---- ransac.cu : K8, RANSAC hypothesis scoring (RansacFitter::process_fundamental_matrix, src/RansacFitter.h:42-98,
+// for nF candidate fundamental matrices at once).  dF: [nF][9] row-major; dx0 / dx1: [npt][3] homogeneous matches.
+// Outputs per hypothesis: ok (the reference's return value), inlier count and camera (3 x 4 row-major) of the
+// winning candidate, and (nullable) its inlier bitmask, [nF][ceil(npt / 32)] words, bit = match & 31.
+size_t ransac_ws_bytes(int nF, int npt);
+cudaError_t ransac_score(const double* dF, int nF, const double* dx0, const double* dx1, int npt, double required_percent_inliers,
+                         double reprojection_error_allowed, bool find_best_even_in_failure, double singular_value_ratio_allowed,
+                         int32_t* dok, int32_t* dcount, double* dcams, uint32_t* dmasks, void* ws, size_t ws_bytes,
+                         cudaStream_t stream);
 // launch count bookkeeping (bench.py's gpu_launches)
 unsigned long long launches();
 void count_launch(int n = 1);
