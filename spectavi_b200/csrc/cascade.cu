@@ -362,11 +362,14 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-__device__ __forceinline__ void tmem_ld8_i32(uint32_t taddr, int (&v)[8]) {
+
+// 8 accumulator columns of this thread's TMEM lane, NO wait: the caller issues all loads of a table back to back
+// and waits once (one TMEM round trip per table instead of one per 8 columns -- ncu r01 showed the epilogue warps
+// parked on these loads, long_scoreboard 6.1 per issue)
+__device__ __forceinline__ void tmem_ld8_i32_nowait(uint32_t taddr, int* v) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
                : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
 // one table of one row: MP accumulator columns -> code (+ least-confident bits); v = 32 R exactly
@@ -375,33 +378,49 @@ __device__ __forceinline__ void hq_epilogue_table(uint32_t taddr, const int32_t*
                                                   int32_t* code_out, unsigned long long* flip_out) {
   int v[MP];
 #pragma unroll
-  for (int c = 0; c < MP; c += 8) {
-    int t8[8];
-    tmem_ld8_i32(taddr + c, t8);
+  for (int c = 0; c < MP; c += 8) tmem_ld8_i32_nowait(taddr + c, v + c);
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  // the loaded registers are only valid behind the wait: make every later use depend on a statement that is
+  // ordered after it (volatile asm statements keep their order)
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[c + i] = t8[i] - 128 * scol[c + i];
-  }
+  for (int c = 0; c < MP; c += 8)
+    asm volatile("" : "+r"(v[c]), "+r"(v[c + 1]), "+r"(v[c + 2]), "+r"(v[c + 3]), "+r"(v[c + 4]), "+r"(v[c + 5]), "+r"(v[c + 6]), "+r"(v[c + 7]));
+#pragma unroll
+  for (int c = 0; c < MP; ++c) v[c] = v[c] - 128 * scol[c];
   uint32_t code = 0;   // convert_to_hashcode (CascadingHashNn.h:102-111): bit i set iff R(i) >= 0
 #pragma unroll
   for (int b = MP - 1; b >= 0; --b) code = code * 2u + (~(uint32_t)v[b] >> 31);
   code &= (m >= 32) ? 0xFFFFFFFFu : ((1u << m) - 1u);
   *code_out = (int32_t)code;
   if (nb > 0) {
-    // generate_y_candidate_hashcodes (:153-159): the nb smallest (|R|, bit) pairs; |v| < 2^24
+    // generate_y_candidate_hashcodes (:153-159): the nb smallest (|R|, bit) pairs; |v| < 2^24, so
+    // key = |v| * 32 + bit orders them and keys are distinct (the bit index is part of the key)
     uint32_t key[MP];
 #pragma unroll
-    for (int b = 0; b < MP; ++b) key[b] = b < m ? (((uint32_t)(v[b] < 0 ? -v[b] : v[b]) << 5) | (uint32_t)b) : 0xFFFFFFFFu;
+    for (int b = 0; b < MP; ++b) key[b] = b < m ? ((uint32_t)(v[b] < 0 ? -v[b] : v[b]) * 32u + (uint32_t)b) : 0xFFFFFFFFu;
     unsigned long long flips = 0;
-    uint32_t last = 0;   // keys are distinct (the bit index is part of the key): take them in increasing order
-    for (int q = 0; q < nb; ++q) {
-      uint32_t best = 0xFFFFFFFFu;
+    if (nb <= 2) {
+      // the default probe depth (g = 2): both minima in ONE pass, 3 min / max per key
+      uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
 #pragma unroll
       for (int b = 0; b < MP; ++b) {
-        const uint32_t k = (q == 0 || key[b] > last) ? key[b] : 0xFFFFFFFFu;
-        best = k < best ? k : best;
+        m2 = min(m2, max(m1, key[b]));
+        m1 = min(m1, key[b]);
       }
-      last = best;
-      flips |= (unsigned long long)(best & 31u) << (5 * q);
+      flips = (unsigned long long)(m1 & 31u);
+      if (nb == 2) flips |= (unsigned long long)(m2 & 31u) << 5;
+    } else {
+      uint32_t last = 0;   // take the keys in increasing order
+      for (int q = 0; q < nb; ++q) {
+        uint32_t best = 0xFFFFFFFFu;
+#pragma unroll
+        for (int b = 0; b < MP; ++b) {
+          const uint32_t k = (q == 0 || key[b] > last) ? key[b] : 0xFFFFFFFFu;
+          best = k < best ? k : best;
+        }
+        last = best;
+        flips |= (unsigned long long)(best & 31u) << (5 * q);
+      }
     }
     *flip_out = flips;
   }

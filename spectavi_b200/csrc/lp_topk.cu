@@ -172,6 +172,22 @@ __global__ void __launch_bounds__(NT, 2) lp_topk_kernel(const LpParams P) {
         const float4* xp = reinterpret_cast<const float4*>(xs + c * PITCH + tx * 4);
         *reinterpret_cast<float4*>(&ya[0]) = yp[0]; *reinterpret_cast<float4*>(&ya[4]) = yp[1];
         *reinterpret_cast<float4*>(&xb[0]) = xp[0]; *reinterpret_cast<float4*>(&xb[4]) = xp[TB / 8];   // + 64 rows
+        if constexpr (std::is_same<T, float>::value && (PM == P_ONE || PM == P_TWO)) {
+          // packed FP32 (SASS FADD2 / FMUL2: two IEEE-rn operations per instruction, each lane rounded exactly as the
+          // scalar instruction rounds, so the sums stay bit-identical): the accumulators of two adjacent train rows
+          // share a register pair, the query value is the instruction's scalar-broadcast operand
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+              float2 d = __fadd2_rn(make_float2(xb[2 * jj], xb[2 * jj + 1]), make_float2(-ya[i], -ya[i]));   // x - y (:68)
+              if (PM == P_ONE) d = make_float2(fabsf(d.x), fabsf(d.y));
+              else d = __fmul2_rn(d, d);
+              const float2 a2 = __fadd2_rn(make_float2(acc[i][2 * jj], acc[i][2 * jj + 1]), d);             // :70-79
+              acc[i][2 * jj] = a2.x;
+              acc[i][2 * jj + 1] = a2.y;
+            }
+        } else
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
