@@ -186,6 +186,9 @@ int spv_normalize_device(const float *dx, int rows, int dim, float *dout_f32, ui
  * didx: yrows x k uint64, ddist: yrows x k float32 / int32, ascending, right-aligned and zero-filled in front
  * when xrows < k (what nn_bruteforce returns into numpy zeros).  dws: spv_nn_bruteforce_ws_bytes() of scratch. */
 size_t spv_nn_bruteforce_ws_bytes(int xrows, int yrows, int k);
+/* the same plus room for the TMA-fed float32 kernel's column-major copies of both matrices: with this much
+ * scratch float32 rows (k <= 128) take the faster kernel; results are identical either way */
+size_t spv_nn_bruteforce_ws_bytes_dim(int xrows, int yrows, int dim, int k);
 int spv_nn_bruteforce_device(const void *dx, const void *dy, int is_int, int xrows, int yrows, int dim, int k,
                              double p, uint64_t *didx, void *ddist, void *dws, size_t ws_bytes, void *stream);
 

@@ -128,13 +128,18 @@ size_t spv_nn_bruteforce_ws_bytes(int xrows, int yrows, int k) {
   return lp_partial_bytes(xrows, yrows, k, sms) + 8;
 }
 
+size_t spv_nn_bruteforce_ws_bytes_dim(int xrows, int yrows, int dim, int k) {
+  const int sms = sm_count();
+  if (sms <= 0 || xrows < 0 || yrows < 0 || dim < 1 || k < 1) return 0;
+  return lp_ws_bytes(xrows, yrows, dim, k, sms);
+}
+
 int spv_nn_bruteforce_device(const void* dx, const void* dy, int is_int, int xrows, int yrows, int dim, int k, double p,
                              uint64_t* didx, void* ddist, void* dws, size_t ws_bytes, void* stream) {
   if (xrows < 0 || yrows < 0 || dim <= 0) return fail("bad shape %d x %d x %d", xrows, yrows, dim);
   if (k < 1) return fail("k = %d must be >= 1", k);
   if (ws_bytes < spv_nn_bruteforce_ws_bytes(xrows, yrows, k)) return fail("workspace too small");
-  CU_OR_FAIL(lp_topk(dx, dy, is_int != 0, xrows, yrows, dim, k, p, reinterpret_cast<unsigned long long*>(dws), didx, ddist,
-                     (cudaStream_t)stream));
+  CU_OR_FAIL(lp_topk(dx, dy, is_int != 0, xrows, yrows, dim, k, p, dws, ws_bytes, didx, ddist, (cudaStream_t)stream));
   return 0;
 }
 

@@ -534,13 +534,13 @@ void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yro
   const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
   CU(fn_, D.x.ensure(xb ? xb : 4));
   CU(fn_, D.y.ensure(yb ? yb : 4));
-  CU(fn_, D.gather.ensure(lp_partial_bytes(xrows, yrows, k, sms) + 8));
+  CU(fn_, D.gather.ensure(lp_ws_bytes(xrows, yrows, dim, k, sms)));
   CU(fn_, D.oidx.ensure(ib));
   CU(fn_, D.odist.ensure(db));
   if (xb) CU(fn_, cudaMemcpyAsync(D.x.p, x, xb, cudaMemcpyHostToDevice, D.stream));
   CU(fn_, cudaMemcpyAsync(D.y.p, y, yb, cudaMemcpyHostToDevice, D.stream));
-  CU(fn_, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, (unsigned long long*)D.gather.p, (uint64_t*)D.oidx.p,
-                  D.odist.p, D.stream));
+  CU(fn_, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p, D.odist.p,
+                  D.stream));
   CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaStreamSynchronize(D.stream));

@@ -534,6 +534,20 @@ bool make_rows_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// column-major float32 matrix [dim][pitch] (pitch floats per column, rows valid), seen as 2-D (rows, dim); a box of
+// (box_rows, box_cols) lands in shared memory as [col][row]; rows / columns outside the matrix read as zeros
+bool make_f32_panel_map(CUtensorMap* map, const float* base, int rows, int dim, size_t pitch, int box_rows, int box_cols) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)(rows > 0 ? rows : 1), (cuuint64_t)dim};
+  cuuint64_t gstride[1] = {(cuuint64_t)pitch * 4u};
+  cuuint32_t box[2] = {(cuuint32_t)box_rows, (cuuint32_t)box_cols};
+  cuuint32_t estr[2] = {1u, 1u};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 namespace {
 
 cudaError_t launch_tiled(const CUtensorMap& tmx, const CUtensorMap& tmy, Params p, int sms, cudaStream_t stream) {

@@ -31,6 +31,8 @@
 #include "spv_common.h"
 
 #include <cstdint>
+#include <cstdlib>
+#include <cstring>
 #include <type_traits>
 
 namespace spv {
@@ -421,8 +423,14 @@ size_t lp_partial_bytes(int xrows, int yrows, int k, int sms) {
   return lists + (k > LP_MAX_K ? (size_t)(yrows > 0 ? yrows : 0) * sizeof(unsigned long long) : 0);
 }
 
+size_t lp_ws_bytes(int xrows, int yrows, int dim, int k, int sms) {
+  const size_t a = lp_partial_bytes(xrows, yrows, k, sms) + 8, b = lp_tma_ws_bytes(xrows, yrows, dim, k, sms);
+  return a > b ? a : b;
+}
+
 cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
-                    unsigned long long* partial, uint64_t* didx, void* ddist, cudaStream_t stream) {
+                    void* ws, size_t ws_bytes, uint64_t* didx, void* ddist, cudaStream_t stream) {
+  unsigned long long* partial = static_cast<unsigned long long*>(ws);
   if (yrows <= 0) return cudaSuccess;
   if (k < 1 || dim < 1) return cudaErrorInvalidValue;
   // the caller's arrays start as zeros (numpy), and unfilled columns stay zero
@@ -433,6 +441,21 @@ cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int 
   int dev = 0, sms = 0;
   if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
   if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  if (!is_int && k <= LP_MAX_K) {
+    // float32 rows: the TMA-fed kernel (lp_topk_tma.cu) when the caller's scratch admits its transposed copies
+    const char* force = getenv("SPECTAVI_K1F");
+    const size_t need = lp_tma_ws_bytes(xrows, yrows, dim, k, sms);
+    if (!(force && strcmp(force, "v1") == 0) && need && ws_bytes >= need) {
+      unsigned long long* tp = nullptr;
+      int tsplits = 1;
+      e = lp_topk_tma((const float*)dx, (const float*)dy, xrows, yrows, dim, k, p, ws, ws_bytes, sms, &tp, &tsplits, stream);
+      if (e != cudaSuccess) return e;
+      lp_merge_kernel<float><<<(yrows + 127) / 128, 128, 0, stream>>>(tp, tsplits, yrows, k, didx, (float*)ddist);
+      count_launch();
+      return cudaGetLastError();
+    }
+  }
+  if (ws_bytes < lp_partial_bytes(xrows, yrows, k, sms)) return cudaErrorInvalidValue;
   LpParams P;
   P.x = dx; P.y = dy; P.xrows = xrows; P.yrows = yrows; P.dim = dim; P.k = k; P.p = p;
   P.nxt = (xrows + TB - 1) / TB;

@@ -48,13 +48,22 @@ cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kco
 // a box of (16, box_rows, dim/16) lands in shared memory as [dim/16][box_rows][16 B], i.e. already in the
 // k-chunk-major order K1 reads and in the UMMA K-major no-swizzle core-matrix order K2 feeds to tcgen05
 bool make_rows_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows);
+bool make_f32_panel_map(CUtensorMap* map, const float* base, int rows, int dim, size_t pitch, int box_rows, int box_cols);
 // ---- lp_topk.cu : K1f, brute-force sum |x-y|^p top-k over float32 / int32 rows
 // (BruteForceNn.h:37-120).  partial: scratch of lp_partial_bytes(); didx/ddist:
 // yrows x k outputs in the reference's layout (ascending, right-aligned).
 constexpr int LP_MAX_K = 128;
-size_t lp_partial_bytes(int xrows, int yrows, int k, int sms);
+size_t lp_partial_bytes(int xrows, int yrows, int k, int sms);     // scratch of the register-staged kernel (any dtype, any k)
+// scratch that also admits the TMA-fed kernel (lp_topk_tma.cu: float32 rows, k <= LP_MAX_K): >= lp_partial_bytes
+size_t lp_ws_bytes(int xrows, int yrows, int dim, int k, int sms);
+// ws_bytes decides the kernel: with lp_ws_bytes() of scratch float32 rows take the TMA-fed kernel (unless the
+// environment says SPECTAVI_K1F=v1), otherwise -- and for int32 rows, k > LP_MAX_K -- the register-staged one
 cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
-                    unsigned long long* partial, uint64_t* didx, void* ddist, cudaStream_t stream);
+                    void* ws, size_t ws_bytes, uint64_t* didx, void* ddist, cudaStream_t stream);
+// lp_topk_tma.cu
+size_t lp_tma_ws_bytes(int xrows, int yrows, int dim, int k, int sms);
+cudaError_t lp_topk_tma(const float* dx, const float* dy, int xrows, int yrows, int dim, int k, double p, void* ws,
+                        size_t ws_bytes, int sms, unsigned long long** partial_out, int* splits_out, cudaStream_t stream);
 // The filter overload (BruteForceNn.h:37-49), batched: tile t = {ypos, ycnt <= lp_filtered_tile_rows(), xpos, xcnt}
 // searches query rows ysel[ypos .. ypos+ycnt) among train rows xsel[xpos .. xpos+xcnt).  A query row id may appear
 // in ysel once.  didx / ddist (yrows x k) are in-out: only rows named by ysel are written, right-aligned.

@@ -130,6 +130,8 @@ def normalize_rows(x, want_f32=True, want_u8=True):
 
 clib.spv_nn_bruteforce_ws_bytes.restype = ct.c_size_t
 clib.spv_nn_bruteforce_ws_bytes.argtypes = [ct.c_int, ct.c_int, ct.c_int]
+clib.spv_nn_bruteforce_ws_bytes_dim.restype = ct.c_size_t
+clib.spv_nn_bruteforce_ws_bytes_dim.argtypes = [ct.c_int, ct.c_int, ct.c_int, ct.c_int]
 clib.spv_nn_bruteforce_device.restype = ct.c_int
 clib.spv_nn_bruteforce_device.argtypes = [_vp, _vp, ct.c_int, ct.c_int, ct.c_int, ct.c_int, ct.c_int, ct.c_double, _vp, _vp,
                                           _vp, ct.c_size_t, _vp]
@@ -142,7 +144,7 @@ def nn_bruteforce(x, y, p=.5, k=2):
     assert x.is_contiguous() and y.is_contiguous() and x.dim() == 2 and y.dim() == 2 and x.shape[1] == y.shape[1]
     xrows, dim = x.shape
     yrows = y.shape[0]
-    nbytes = int(clib.spv_nn_bruteforce_ws_bytes(xrows, yrows, k))
+    nbytes = int(clib.spv_nn_bruteforce_ws_bytes_dim(xrows, yrows, dim, k))
     if nbytes == 0:
         raise ValueError("unsupported k")
     ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)

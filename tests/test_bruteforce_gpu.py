@@ -151,3 +151,27 @@ def test_bruteforce_k_above_128(po, feature, xr, k, use_int):
     else:
         oi, od = po.bruteforce(x, y, k, 1., 0.)
         assert (gi == oi).all() and (gd.view(np.uint32) == od.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("shape,k", [((3000, 700, 132), 2), ((777, 129, 5), 7), ((300, 300, 33), 128), ((5000, 64, 16), 1)])
+@pytest.mark.parametrize("p", [1., 2., .5, 1.5])
+def test_bruteforce_tma_kernel_equals_register_staged_kernel(po, feature, shape, k, p):
+    """float32 rows take the TMA-fed kernel (lp_topk_tma.cu: column-major copies, producer warp, packed FADD2);
+    SPECTAVI_K1F=v1 forces the register-staged one.  Same operations in the same order: identical bits, ragged
+    tiles / panels included (TMA zero fill adds +0.0)."""
+    import os
+    xr, yr, dim = shape
+    rng = np.random.RandomState(xr + k)
+    x = rng.randn(xr, dim).astype("float32")
+    y = rng.randn(yr, dim).astype("float32")
+    os.environ.pop("SPECTAVI_K1F", None)
+    gi, gd = feature.nn_bruteforce(x, y, p=p, mu=0., k=k)
+    os.environ["SPECTAVI_K1F"] = "v1"
+    try:
+        vi, vd = feature.nn_bruteforce(x, y, p=p, mu=0., k=k)
+    finally:
+        os.environ.pop("SPECTAVI_K1F", None)
+    assert (gi == vi).all() and (gd.view(np.uint32) == vd.view(np.uint32)).all()
+    if p != 1.5:
+        oi, od = po.bruteforce(x, y, k, p, 0.)
+        assert (gi.reshape(oi.shape) == oi).all() and (gd.reshape(od.shape).view(np.uint32) == od.view(np.uint32)).all()
