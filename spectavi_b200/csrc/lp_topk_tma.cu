@@ -92,6 +92,48 @@ __device__ __forceinline__ bool cbar_or(bool pred) {
   return r != 0;
 }
 
+// Packed FP32 through explicit PTX.  ptxas (12.9) contracts `mul.rn.f32x2` + `add.rn.f32x2` into one FFMA2 although
+// both carry an explicit rounding modifier (it also sees through fma(d, d, -0) and through the __fmul2_rn /
+// __fadd2_rn intrinsics) -- measured: FFMA2 in the p = 2 kernel and last-place differences against the reference,
+// which is built without FMA.  The scalar `mul.rn.f32` IS respected, so the square is two scalar FMULs on the
+// unpacked halves between the packed subtraction and the packed accumulation: 4 instructions per two
+// pair-columns instead of 6, bit-exact (profiles/r02_sass_opcodes.txt: no FFMA2 / FFMA in these kernels).
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long add2_rn(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long sub2_rn(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// acc(2 lanes) += term(x(2 lanes) - y): |d| for P1, d * d otherwise; every operation IEEE-rn per lane
+template <bool P1>
+__device__ __forceinline__ void pair_step(float& a0, float& a1, float x0, float x1, float y) {
+  unsigned long long d = sub2_rn(pk2(x0, x1), pk2(y, y));
+  if (P1) {
+    float d0, d1;
+    upk2(d, d0, d1);
+    d = pk2(fabsf(d0), fabsf(d1));
+  } else {
+    float d0, d1;
+    upk2(d, d0, d1);
+    asm("mul.rn.f32 %0, %0, %0;" : "+f"(d0));
+    asm("mul.rn.f32 %0, %0, %0;" : "+f"(d1));
+    d = pk2(d0, d1);
+  }
+  upk2(add2_rn(pk2(a0, a1), d), a0, a1);
+}
+
 template <int PM>
 __device__ __forceinline__ float term_f(float d, double p) {
   if (PM == P_ONE) return fabsf(d);
@@ -205,12 +247,7 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
           for (int i = 0; i < 8; ++i)
 #pragma unroll
             for (int jj = 0; jj < 4; ++jj) {
-              float2 d = __fadd2_rn(make_float2(xb[2 * jj], xb[2 * jj + 1]), make_float2(-ya[i], -ya[i]));   // x - y (BruteForceNn.h:68)
-              if (PM == P_ONE) d = make_float2(fabsf(d.x), fabsf(d.y));
-              else d = __fmul2_rn(d, d);
-              const float2 a2 = __fadd2_rn(make_float2(acc[i][2 * jj], acc[i][2 * jj + 1]), d);             // :70-79
-              acc[i][2 * jj] = a2.x;
-              acc[i][2 * jj + 1] = a2.y;
+              pair_step<PM == P_ONE>(acc[i][2 * jj], acc[i][2 * jj + 1], xb[2 * jj], xb[2 * jj + 1], ya[i]);   // BruteForceNn.h:68-79
             }
         } else {
 #pragma unroll

@@ -44,7 +44,7 @@ enum Variant {
   V_FSUB_FMUL_FADD,    // FADD d ; FMUL d*d ; FADD acc         (K1f's p = 2 pair-column, no FMA contraction)
   V_FADD2,             // add.rn.f32x2 (SASS FADD2): two IEEE-rn float adds per instruction
   V_F2_SUB_ABSADD,     // FADD2 d, a, -b ; FADD2 acc, acc, |d|  (two p = 1 pair-columns per instruction pair)
-  V_F2_SUB_MUL_ADD,    // FADD2 ; FMUL2 ; FADD2                 (two p = 2 pair-columns per instruction triple)
+  V_F2_SUB_MUL_ADD,    // FADD2 ; FMUL ; FMUL ; FADD2           (two p = 2 pair-columns per four instructions)
   V_DFMA,              // fma.rn.f64
   V_DMUL_DADD,         // mul.rn.f64 ; add.rn.f64               (K8's arithmetic: no contraction, ransac.cu)
   V_COUNT
@@ -190,8 +190,11 @@ __global__ void __launch_bounds__(256, 2) peak_kernel(const uint32_t* __restrict
         float2 x = make_float2(__uint_as_float(a[i & 7]), __uint_as_float(a[(i + 1) & 7]));
         float2 y = make_float2(__uint_as_float(acc[o]), __uint_as_float(acc[o + 1]));
         float2 c = make_float2(__uint_as_float(acc[i]), __uint_as_float(acc[i + 1]));
+        // the form K1f uses: ptxas contracts a packed multiply + packed add into FFMA2 even with .rn, which would not be
+        // bit-exact; the square is two scalar FMULs between the packed subtraction and the packed accumulation
         float2 d = __fadd2_rn(x, make_float2(-y.x, -y.y));
-        d = __fmul2_rn(d, d);
+        asm volatile("mul.rn.f32 %0, %0, %0;" : "+f"(d.x));
+        asm volatile("mul.rn.f32 %0, %0, %0;" : "+f"(d.y));
         c = __fadd2_rn(c, d);
         acc[i] = __float_as_uint(c.x); acc[i + 1] = __float_as_uint(c.y);
       }
@@ -240,7 +243,7 @@ const Desc kDesc[V_COUNT] = {
   {"f32 sub + mul + add (FADD FMUL FADD)", NACC, 1},
   {"FADD2 (add.rn.f32x2)", NACC / 2, 2},                        // op = one instruction = two float adds
   {"f32x2 sub + |.|add (2 FADD2 per 2)", NACC, 1},               // op = one p = 1 pair-column
-  {"f32x2 sub + mul + add (FADD2 FMUL2 FADD2 per 2)", NACC, 1},  // op = one p = 2 pair-column
+  {"f32x2 sub + mul + add (FADD2 2xFMUL FADD2 per 2)", NACC, 1},  // op = one p = 2 pair-column
   {"DFMA", NACC / 2, 1},
   {"f64 mul + add (DMUL DADD)", NACC / 2, 1},                    // op = one multiply-add pair, not contracted
 };
