@@ -205,6 +205,10 @@ size_t spv_cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g);
 int spv_cascade_device(const uint8_t *dxu8, const uint8_t *dyu8, int xrows, int yrows, int dim, int m, int n, int g,
                        const float *ddict, int dict_terms, uint32_t xoffset, uint64_t *dkeys, void *dws,
                        size_t ws_bytes, void *stream);
+/* With SPECTAVI_STAGE_TIMING=1 in the environment spv_cascade_device records CUDA events at its stage boundaries;
+ * this returns the milliseconds of {dictionary image, K2 train side, K3 buckets, K2 query side, K4} of the calling
+ * thread's last call (5 values; returns the count, 0 when timing is off).  Synchronises on the last event. */
+int spv_cascade_stage_ms(double *out, int n);
 /* K2 alone: hash codes [n][rows] int32 of uint8 (value + 128) rows (replaces
  * generate_hashcodes_for_data, CascadingHashNn.h:125-135) and, when g > 0, the
  * min(g, m) least-confident bit positions of every (table, row), 5 bits each

@@ -182,6 +182,8 @@ int spv_ransac_score_device(const double* dF, int nF, const double* dx0, const d
   return 0;
 }
 
+int spv_cascade_stage_ms(double* out, int n) { return cascade_stage_ms(out, n); }
+
 void spv_cascade_dictionary(unsigned seed, int dim, int m, int n, int quantize, float* out) {
   cascade_dictionary(seed, dim, m, n, quantize != 0, out);
 }

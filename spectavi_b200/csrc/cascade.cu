@@ -25,6 +25,7 @@
 
 #include <cuda_bf16.h>
 #include <cstdint>
+#include <cstdlib>
 
 namespace spv {
 namespace {
@@ -1083,6 +1084,39 @@ cudaError_t hash_codes(const uint8_t* drows, int rows, int dim, int m, int n, in
   return run_project(pl, drows, rows, dim, n, m, g > 0 ? pl.nb : 0, img, codes, flips, sms, stream);
 }
 
+// Optional stage timing (SPECTAVI_STAGE_TIMING=1): CUDA events on the launching stream at the stage boundaries of the
+// calling thread's last cascade_match; read back with cascade_stage_ms().  Stages: dictionary image, K2 train side,
+// K3 (count + scan + scatter), K2 query side, K4.
+namespace {
+constexpr int NSTAGE = 5;
+thread_local cudaEvent_t t_ev[NSTAGE + 1];
+thread_local bool t_ev_made = false, t_ev_valid = false;
+bool stage_timing_on() {
+  static const bool on = getenv("SPECTAVI_STAGE_TIMING") != nullptr;
+  return on;
+}
+void stage_mark(int i, cudaStream_t stream) {
+  if (!stage_timing_on()) return;
+  if (!t_ev_made) {
+    for (int e = 0; e <= NSTAGE; ++e) cudaEventCreate(&t_ev[e]);
+    t_ev_made = true;
+  }
+  cudaEventRecord(t_ev[i], stream);
+  if (i == NSTAGE) t_ev_valid = true;
+}
+}  // namespace
+
+int cascade_stage_ms(double* out, int n) {
+  if (!t_ev_valid || n < NSTAGE) return 0;
+  if (cudaEventSynchronize(t_ev[NSTAGE]) != cudaSuccess) return 0;
+  for (int i = 0; i < NSTAGE; ++i) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, t_ev[i], t_ev[i + 1]) != cudaSuccess) return 0;
+    out[i] = ms;
+  }
+  return NSTAGE;
+}
+
 cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, int yrows, int dim, int m, int n, int g,
                           const float* ddict, int dict_terms, uint32_t xoffset, unsigned long long* keys, void* ws,
                           size_t ws_bytes, cudaStream_t stream) {
@@ -1104,10 +1138,13 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
   int32_t* ids = reinterpret_cast<int32_t*>(w + pl.o_ids);
   uint32_t* sums = reinterpret_cast<uint32_t*>(w + pl.o_sums);
 
+  stage_mark(0, stream);
   build_image(pl, ddict, n, dim, m, img, stream);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  stage_mark(1, stream);
   // train side: codes, then CSR buckets (initialize_hash_tables, :187-196)
   if ((e = run_project(pl, dxu8, xrows, dim, n, m, 0, img, xcodes, nullptr, sms, stream)) != cudaSuccess) return e;
+  stage_mark(2, stream);
   if ((e = cudaMemsetAsync(cursor, 0, pl.ncursor * 4, stream)) != cudaSuccess) return e;
   const size_t total = (size_t)n * xrows;
   const uint32_t mask = (1u << pl.mb) - 1u;
@@ -1118,9 +1155,11 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
   bucket_scatter_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(xcodes, total, xrows, mask, pl.mb, cursor, ids);
   count_launch(5);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  stage_mark(3, stream);
   // query side: codes + least-confident bits, then probe / gather / re-rank
   if ((e = run_project(pl, dyu8, yrows, dim, n, m, pl.nb > 0 ? pl.nb : 0, img, ycodes, yflips, sms, stream)) != cudaSuccess) return e;
   if (pl.nb == 0 && (e = cudaMemsetAsync(yflips, 0, (size_t)n * yrows * 8, stream)) != cudaSuccess) return e;
+  stage_mark(4, stream);
   PrParams pr;
   pr.xu8 = dxu8; pr.yu8 = dyu8; pr.xcodes = xcodes; pr.ycodes = ycodes; pr.yflips = yflips; pr.cursor = cursor; pr.ids = ids;
   pr.xrows = xrows; pr.yrows = yrows; pr.dim = dim; pr.n = n; pr.m = m; pr.mb = pl.mb; pr.nb = pl.nb; pr.xoffset = xoffset;
@@ -1134,6 +1173,7 @@ cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, i
     default: probe_rerank_kernel<0><<<prgrid, PR_WARPS * 32, 0, stream>>>(pr); break;
   }
   count_launch();
+  stage_mark(5, stream);
   return cudaGetLastError();
 }
 

@@ -6,6 +6,7 @@
 #include <dlfcn.h>
 #include <nccl.h>   // types only; the library is dlopen()ed when SPECTAVI_GPUS > 1
 
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <random>
@@ -151,6 +152,18 @@ void init_runtime(const char* fn) {   // g_rt.mu held
   g_rt.ready = true;
 }
 
+// ---- optional host-side timeline (SPECTAVI_TRACE=1): one stderr line per step, milliseconds since the call began
+struct Trace {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  Trace() : on(getenv("SPECTAVI_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+  void operator()(const char* what, long long a = 0, long long b = 0) const {
+    if (!on) return;
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    fprintf(stderr, "[spv trace] %8.3f ms  %s %lld %lld\n", ms, what, a, b);
+  }
+};
+
 // ---- staged uploads ------------------------------------------------------------------------------------
 void lanes_init(const char* fn, Gpu& D) {
   if (D.lanes_ready) return;
@@ -205,8 +218,10 @@ std::vector<int> piece_rows(int rows, int first, int cap, int align) {
 // each against all query rows.  K1 folds into one key buffer across launches (xoffset) and seeds its thresholds
 // from it (l1_top2.cu), so the chunking costs no extra slow-path work.  Nothing is synchronised here.
 void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* y, int x0, int xn, int yrows, int dim) {
+  const Trace tr;
   CU(fn, cudaSetDevice(D.dev));
   lanes_init(fn, D);
+  tr("lanes ready");
   const size_t ybytes = (size_t)yrows * dim, kbytes = (size_t)2 * yrows * sizeof(unsigned long long);
   CU(fn, D.y.ensure(ybytes));
   CU(fn, D.keys.ensure(kbytes));
@@ -220,12 +235,15 @@ void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* 
   uint8_t* dx = (uint8_t*)D.x.p;
   uint8_t* dy = (uint8_t*)D.y.p;
   unsigned long long* dk = (unsigned long long*)D.keys.p;
+  tr("buffers ready");
   lane_upload(fn, L, dx, x + (size_t)x0 * dim, (size_t)xp[0] * dim);
+  tr("x piece queued", xp[0]);
   int yo = 0;
   for (int rows : yp) {
     lane_upload(fn, L, dy + (size_t)yo * dim, y + (size_t)yo * dim, (size_t)rows * dim);
     CU(fn, cudaStreamWaitEvent(D.stream, L.ready, 0));
     CU(fn, l1_top2_u8(dx, dy + (size_t)yo * dim, xp[0], rows, dim, (uint32_t)x0, dk + yo, D.stream, yrows));
+    tr("y piece queued + K1 launched", rows);
     yo += rows;
   }
   int xo = xp[0];
@@ -233,6 +251,7 @@ void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* 
     lane_upload(fn, L, dx + (size_t)xo * dim, x + (size_t)(x0 + xo) * dim, (size_t)xp[i] * dim);
     CU(fn, cudaStreamWaitEvent(D.stream, L.ready, 0));
     CU(fn, l1_top2_u8(dx + (size_t)xo * dim, dy, xp[i], yrows, dim, (uint32_t)(x0 + xo), dk, D.stream, yrows));
+    tr("x piece queued + K1 launched", xp[i]);
     xo += xp[i];
   }
 }
@@ -373,6 +392,7 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
     const int xn = (x0 + per <= xrows) ? per : xrows - x0;
     l1k2_stream_shard(fn, c.gpus[g], x, y, x0, xn, yrows, dim);
   });
+  const Trace tr;
   merge_shards(fn_, c, yrows);
   if (ms) {
     deliver_matches(*ms, yrows, false);
@@ -380,6 +400,7 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
   }
   Gpu& R = c.gpus[0];
   CU(fn_, cudaSetDevice(R.dev));
+  if (tr.on) { CU(fn_, cudaStreamSynchronize(R.stream)); tr("(trace only) K1 launches drained"); }
   CU(fn_, R.oidx.ensure((size_t)yrows * 2 * sizeof(uint64_t)));
   CU(fn_, R.odist.ensure((size_t)yrows * 2 * sizeof(int32_t)));
   CU(fn_, keys_finalize_i32((const unsigned long long*)R.keys.p, yrows, 2, (uint64_t*)R.oidx.p, (int32_t*)R.odist.p,
@@ -387,6 +408,7 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
   CU(fn_, cudaMemcpyAsync(idx, R.oidx.p, (size_t)yrows * 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, R.stream));
   CU(fn_, cudaMemcpyAsync(dist, R.odist.p, (size_t)yrows * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, R.stream));
   sync_all(fn_, c);
+  tr("results on the host");
 }
 
 void cascade_dictionary(unsigned seed, int dim, int m, int n, bool quantize, float* out) {

@@ -151,6 +151,9 @@ __device__ __forceinline__ void fold_key(unsigned long long* keys, long long kst
 // real distance (BruteForceNnL1K2.h:99-103).
 __device__ __forceinline__ uint32_t thr_of(unsigned long long second) {
   const uint32_t d2 = (uint32_t)(second >> 32);
+#ifdef SPV_K1_STRICT       // (A/B builds only) round 1's strict threshold: valid only without seeding
+  return d2 < THR_MAX ? d2 : THR_MAX;
+#endif
   return d2 < THR_MAX ? d2 + 1u : THR_MAX;
 }
 
@@ -300,7 +303,9 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
       {
         const int srow = yt * BY + warp * 32 + lane;
         unsigned long long s1 = KEY_NONE, s2 = KEY_NONE;
+#ifndef SPV_K1_NO_SEED   // (A/B builds only: tools/gpu_r2_c.sh)
         if (srow < p.yrows) { s1 = __ldcg(p.keys + srow); s2 = __ldcg(p.keys + p.kstride + srow); }
+#endif
         st[lane] = s1;
         st[BY + lane] = s2;
       }

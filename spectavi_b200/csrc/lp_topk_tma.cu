@@ -18,9 +18,8 @@
 //   * one CTA of 9 warps per SM: up to 224 registers per thread, no spills;
 //   * ragged edges cost nothing: TMA zero-fills rows / columns outside the matrix, a zero column adds +0.0 to
 //     every accumulator (exact), padded rows are masked where candidates are selected.
-// The selection part (per-row sorted lists, candidate queue, first-tile bound) is lp_topk.cu's, with the CTA-wide
-// barriers replaced by a named barrier over the 256 compute threads (the producer keeps prefetching the next
-// train tile's panels while the compute warps select).
+// Selection (per-row sorted lists, first-tile bound) is warp-local: a warp owns its 16 query rows outright, so there is
+// no CTA-wide barrier anywhere after start-up and the warps drift apart like K1's.
 #include "spv_common.h"
 
 #include <cuda.h>
@@ -34,7 +33,6 @@ constexpr int KC = 16;           // columns per stage
 constexpr int NCW = 8;           // compute warps
 constexpr int NCT = NCW * 32;    // compute threads
 constexpr int NT = NCT + 32;     // + the producer warp
-constexpr int QCAP = 1024;
 constexpr uint32_t THR_NONE = 0xFFFFFFFFu;
 constexpr int STAGE_FLOATS = 2 * KC * TB;   // x panel then y panel, [col][row]
 
@@ -77,21 +75,6 @@ __device__ __forceinline__ void tma_load_panel(uint32_t dst, const CUtensorMap* 
       ::"r"(dst), "l"(map), "r"(row0), "r"(col0), "r"(bar)
       : "memory");
 }
-// named barrier over the compute threads only (id 1); the producer warp never joins
-__device__ __forceinline__ void cbar() { asm volatile("bar.sync 1, %0;" ::"n"(NCT) : "memory"); }
-__device__ __forceinline__ bool cbar_or(bool pred) {
-  uint32_t r;
-  asm volatile(
-      "{\n\t.reg .pred q, r;\n\t"
-      "setp.ne.u32 q, %1, 0;\n\t"
-      "bar.red.or.pred r, 1, %2, q;\n\t"
-      "selp.u32 %0, 1, 0, r;\n\t}"
-      : "=r"(r)
-      : "r"((uint32_t)pred), "n"(NCT)
-      : "memory");
-  return r != 0;
-}
-
 // Packed FP32 through explicit PTX.  ptxas (12.9) contracts `mul.rn.f32x2` + `add.rn.f32x2` into one FFMA2 although
 // both carry an explicit rounding modifier (it also sees through fma(d, d, -0) and through the __fmul2_rn /
 // __fadd2_rn intrinsics) -- measured: FFMA2 in the p = 2 kernel and last-place differences against the reference,
@@ -176,10 +159,7 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
   float* ring = reinterpret_cast<float*>(smem_raw);                                  // [nst][x panel | y panel][KC][TB]
   uint32_t* thr = reinterpret_cast<uint32_t*>(ring + (size_t)nst * STAGE_FLOATS);   // [TB] k-th best distance bits
   int* cnt = reinterpret_cast<int*>(thr + TB);                                       // [TB] entries in each row's list
-  unsigned long long* qkey = reinterpret_cast<unsigned long long*>(cnt + TB);        // [QCAP]
-  unsigned short* qrow = reinterpret_cast<unsigned short*>(qkey + QCAP);             // [QCAP]
-  int* qn = reinterpret_cast<int*>(qrow + QCAP);                                     // [4]
-  unsigned long long* list = reinterpret_cast<unsigned long long*>(qn + 4);          // [TB][k] ascending
+  unsigned long long* list = reinterpret_cast<unsigned long long*>(cnt + TB);        // [TB][k] ascending
   unsigned long long* bars = list + (size_t)TB * k;                                  // full[nst], empty[nst]
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nst;
 
@@ -216,8 +196,8 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
 
   // ===================== compute warps
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-  if (tid < TB) { thr[tid] = THR_NONE; cnt[tid] = 0; }
-  cbar();
+  if (lane < 16) { thr[warp * 16 + lane] = THR_NONE; cnt[warp * 16 + lane] = 0; }   // this warp's rows
+  __syncwarp();
   int stage = 0;
   uint32_t phase = 0;
 
@@ -264,13 +244,19 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
       if (++stage == nst) { stage = 0; phase ^= 1; }
     }
 
-    // ---- selection (lp_topk.cu's, over the 256 compute threads): candidates (dist <= the row's k-th best so far; the
-    // row owner compares whole keys) go through a queue; on the first train tile the k-th smallest of the 16
-    // per-thread minima of a row bounds its k-th distance from above
+    // ---- selection, warp-local.  A warp owns 16 query rows outright (two groups of 16 lanes, 8 rows each, every
+    // lane 8 train rows), so a row's candidates all come from ONE warp and its sorted list needs no CTA-wide
+    // barrier: candidates (dist <= the row's k-th best so far) are handed, one ballot bit at a time, to the
+    // group's first lane, which inserts them into the row's list in shared memory.  Warps therefore drift apart
+    // -- one selects while the others accumulate -- instead of meeting at four barriers per train tile
+    // (measured: with CTA-wide selection and one CTA per SM this kernel was SLOWER than the register-staged one,
+    // 4.84 vs 4.59 ms at 20 k x 20 k x 132: nothing overlapped the selection phase).
     uint32_t thb[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) thb[i] = thr[ty * 8 + i];
     if (t == t0 && k <= 16) {
+      // first train tile: no row has a k-th best yet; the k-th smallest of the 16 per-lane minima of a row bounds
+      // its k-th distance from above
       const int hb = lane & 16;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -286,7 +272,7 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
         }
         const unsigned has = (__ballot_sync(0xFFFFFFFFu, rank == k - 1) >> hb) & 0xFFFFu;   // exactly one lane
         const uint32_t bound = __shfl_sync(0xFFFFFFFFu, mn, hb | (__ffs(has) - 1));
-        if (thb[i] == THR_NONE) thb[i] = bound;     // THR_NONE again when fewer than k threads hold a valid pair
+        if (thb[i] == THR_NONE) thb[i] = bound;     // THR_NONE again when fewer than k lanes hold a valid pair
       }
     }
     unsigned long long pend = 0;
@@ -297,71 +283,53 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
         const bool c = (ty * 8 + i < ycnt) && (x0 + xrow(tx, j) < xcnt) && __float_as_uint(acc[i][j]) <= thb[i];
         pend |= (unsigned long long)c << (i * 8 + j);
       }
-    while (cbar_or(pend != 0)) {
-      if (tid == 0) qn[0] = 0;
-      cbar();
-      {   // one queue reservation per warp
-        const int mine = __popcll(pend);
-        int incl = mine;
+    if (__any_sync(0xFFFFFFFFu, pend != 0)) {
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-          if (lane >= o) incl += v;
-        }
-        int base = 0;
-        if (lane == 31 && incl) base = atomicAdd(&qn[0], incl);
-        int slot = __shfl_sync(0xFFFFFFFFu, base, 31) + incl - mine;
+      for (int i = 0; i < 8; ++i) {
+        const unsigned rm = (unsigned)(pend >> (i * 8)) & 0xFFu;
+        if (!__any_sync(0xFFFFFFFFu, rm != 0)) continue;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if ((pend >> (i * 8 + j)) & 1) {
-              if (slot < QCAP) {
-                qkey[slot] = ((unsigned long long)__float_as_uint(acc[i][j]) << 32) | (uint32_t)(x0 + xrow(tx, j));
-                qrow[slot] = (unsigned short)(ty * 8 + i);
-                pend &= ~(1ull << (i * 8 + j));
+        for (int j = 0; j < 8; ++j) {
+          unsigned b = __ballot_sync(0xFFFFFFFFu, (rm >> j) & 1u);
+          const unsigned long long mykey = ((unsigned long long)__float_as_uint(acc[i][j]) << 32) | (uint32_t)(x0 + xrow(tx, j));
+          while (b) {
+            const int src = __ffs(b) - 1;
+            b &= b - 1;
+            const unsigned long long key = __shfl_sync(0xFFFFFFFFu, mykey, src);
+            if (lane == (src & 16)) {                 // the first lane of the candidate's 16-lane group owns the row's list
+              const int row = (warp * 2 + (src >> 4)) * 8 + i;
+              unsigned long long* L = list + (size_t)row * k;
+              int m = cnt[row];
+              bool take = true;
+              if (m == k) {
+                if (key >= L[k - 1]) take = false;    // beaten meanwhile by an earlier candidate of this tile
+                else --m;                             // drop the current k-th
               }
-              ++slot;
+              if (take) {
+                int pos = m;
+                while (pos > 0 && L[pos - 1] > key) { L[pos] = L[pos - 1]; --pos; }
+                L[pos] = key;
+                ++m;
+                cnt[row] = m;
+                thr[row] = (m == k) ? (uint32_t)(L[k - 1] >> 32) : THR_NONE;
+              }
             }
-      }
-      cbar();
-      const int n = min(qn[0], QCAP);
-      if (tid < TB) {               // thread r owns row r's list
-        unsigned long long* L = list + (size_t)tid * k;
-        int m = cnt[tid];
-        for (int e = 0; e < n; ++e) {
-          if (qrow[e] != tid) continue;
-          const unsigned long long key = qkey[e];
-          if (m == k) {
-            if (key >= L[k - 1]) continue;
-            --m;                     // drop the current k-th
           }
-          int pos = m;
-          while (pos > 0 && L[pos - 1] > key) { L[pos] = L[pos - 1]; --pos; }
-          L[pos] = key;
-          ++m;
-        }
-        cnt[tid] = m;
-        thr[tid] = (m == k) ? (uint32_t)(L[k - 1] >> 32) : THR_NONE;
-      }
-      cbar();
-      if (pend) {   // what is still pending may have been beaten meanwhile
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const uint32_t th = thr[ty * 8 + i];
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (((pend >> (i * 8 + j)) & 1) && __float_as_uint(acc[i][j]) > th) pend &= ~(1ull << (i * 8 + j));
         }
       }
+      __syncwarp();
     }
   }
 
-  // publish this split's sorted lists
-  if (tid < TB && tid < ycnt) {
-    unsigned long long* out = P.partial + ((size_t)blockIdx.y * P.yrows + y0 + tid) * k;
-    const int m = cnt[tid];
-    for (int q = 0; q < k; ++q) out[q] = q < m ? list[(size_t)tid * k + q] : KEY_NONE;
+  // publish this split's sorted lists: every warp its own 16 rows
+  __syncwarp();
+  if (lane < 16) {
+    const int row = warp * 16 + lane;
+    if (row < ycnt) {
+      unsigned long long* out = P.partial + ((size_t)blockIdx.y * P.yrows + y0 + row) * k;
+      const int m = cnt[row];
+      for (int q = 0; q < k; ++q) out[q] = q < m ? list[(size_t)row * k + q] : KEY_NONE;
+    }
   }
 }
 
@@ -386,7 +354,7 @@ int pick_splits_tma(int ny_tiles, int nxt, int sms, size_t rows_times_k) {
   return best;
 }
 
-size_t fixed_smem(int k) { return (size_t)TB * 4 * 2 + QCAP * 8 + QCAP * 2 + 16 + (size_t)TB * k * 8; }
+size_t fixed_smem(int k) { return (size_t)TB * 4 * 2 + (size_t)TB * k * 8; }
 
 template <int PM>
 cudaError_t launch(const CUtensorMap& tmx, const CUtensorMap& tmy, const TmaParams& P, dim3 grid, size_t smem, cudaStream_t stream) {

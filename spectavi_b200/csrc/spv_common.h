@@ -81,6 +81,7 @@ cudaError_t f32_to_u8(const float* din, uint8_t* dout, size_t count, cudaStream_
 cudaError_t cascade_match(const uint8_t* dxu8, const uint8_t* dyu8, int xrows, int yrows, int dim, int m, int n, int g,
                           const float* ddict, int dict_terms, uint32_t xoffset, unsigned long long* keys, void* ws,
                           size_t ws_bytes, cudaStream_t stream);
+int cascade_stage_ms(double* out, int n);   // SPECTAVI_STAGE_TIMING=1: ms of {image, K2 train, K3, K2 query, K4} of the last call
 cudaError_t hash_codes(const uint8_t* drows, int rows, int dim, int m, int n, int g, const float* ddict, int dict_terms,
                        int32_t* codes, unsigned long long* flips, void* ws, size_t ws_bytes, cudaStream_t stream);
 // ---- ratio.cu : K6, ratio test + order-preserving compaction of the surviving matches

@@ -12,7 +12,9 @@ independent uniform rows.  Reports
     a 1-query call and a slice; the C port (oracle_cascade, all host cores) only where _ref is absent.
 run_castle(): the example's default matcher on the example's data (example/ex01_essential_estimation.py:100-101,281):
 the castle pair's SIFT rows through nn_cascading_hash with the auto-m rule; real rows are clustered, so buckets are skewed."""
+import ctypes as ct
 import json, os, sys, time
+os.environ.setdefault("SPECTAVI_STAGE_TIMING", "1")     # events at the cascade's stage boundaries (read once by the library)
 import numpy as np
 import torch
 ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
@@ -64,8 +66,18 @@ def run(rows=1_000_000, dim=128, reps=5, cpu_rows=2000, e2e=True):
     l0 = dev.launch_count()
     ms_c, ((ci, cd), _) = timed(cascade, reps)
     launches = (dev.launch_count() - l0) // (reps + 1)
-    ms_kx, _ = timed(lambda: dev.hash_codes(x, dic, 0, dict_terms=terms), reps)
-    ms_ky, _ = timed(lambda: dev.hash_codes(y, dic, g, dict_terms=terms), reps)
+    # per-stage times of one more call: CUDA events the library records at its stage boundaries
+    from spectavi_b200._libspectavi import clib
+    clib.spv_cascade_stage_ms.restype = ct.c_int
+    clib.spv_cascade_stage_ms.argtypes = [ct.c_void_p, ct.c_int]
+    st = (ct.c_double * 8)()
+    best = None
+    for _ in range(reps):
+        cascade(); torch.cuda.synchronize()
+        if clib.spv_cascade_stage_ms(st, 8) == 5:
+            cur = [st[i] for i in range(5)]
+            best = cur if best is None else [min(a, b) for a, b in zip(best, cur)]
+    ms_img, ms_kx, ms_k3, ms_ky, ms_k4 = best if best else [float("nan")] * 5
 
     bkeys = dev.new_keys(rows, "cuda")
     def brute():
@@ -74,13 +86,24 @@ def run(rows=1_000_000, dim=128, reps=5, cpu_rows=2000, e2e=True):
     r1 = float((ci[:, 0] == bi[:, 0]).float().mean()); r2 = float((ci == bi).float().mean())
     r1p = float((ci[:half, 0] == bi[:half, 0]).float().mean())
     bx, by = rows * (dim + 4 * n), rows * (dim + 12 * n)
+    nb = n << m
+    b3 = n * rows * 16 + nb * 4 * 6          # codes read twice, ids + cursor atomics; counters zeroed, scanned (r + w twice)
+    b4 = rows * (n * (4 + 8) + (n << g) * 8 + 128) + float(rows) * (n << g) * (rows / float(1 << m)) * (4 + dim)   # codes / flips, ranges, query row; ids + candidate rows
+    def stage(ms, nbytes, note=None):
+        d = {"ms": ms, "algorithmic_bytes": int(nbytes), "GBps": nbytes / ms / 1e6, "frac_of_hbm_peak": nbytes / ms / 1e6 / peak}
+        if note:
+            d["note"] = note
+        return d
     out = {"workload": "C5 cascade %d x %d x %d, m=%d n=%d g=%d" % (rows, rows, dim, m, n, g),
            "cascade_ms": ms_c, "queries_per_s": rows / ms_c * 1e3, "effective_Gpairs_per_s": rows * rows / ms_c / 1e6,
            "kernels_per_call": int(launches),
            "stages": {"hbm_peak_GBps": peak, "hbm_peak_source": peak_src,
-                      "K2_train(image + projection + codes)": {"ms": ms_kx, "algorithmic_bytes": bx, "GBps": bx / ms_kx / 1e6, "frac_of_hbm_peak": bx / ms_kx / 1e6 / peak},
-                      "K2_query(+ least-confident bits)": {"ms": ms_ky, "algorithmic_bytes": by, "GBps": by / ms_ky / 1e6, "frac_of_hbm_peak": by / ms_ky / 1e6 / peak},
-                      "K3_K4(buckets + probe / gather / re-rank)": {"ms": ms_c - ms_kx - ms_ky, "note": "remainder of the call; per-kernel split: profiles/ ncu launch list"}},
+                      "timing": "CUDA events recorded by the library at its stage boundaries (SPECTAVI_STAGE_TIMING), best of %d" % reps,
+                      "dictionary_image": {"ms": ms_img},
+                      "K2_train(projection + codes)": stage(ms_kx, bx),
+                      "K3(bucket count + scan + scatter)": stage(ms_k3, b3),
+                      "K2_query(+ least-confident bits)": stage(ms_ky, by),
+                      "K4(probe + gather + re-rank)": stage(ms_k4, b4, "bytes = every candidate row gathered once (no cache reuse assumed); the 126 MB L2 serves about half of them")},
            "bruteforce_ms": ms_b, "bruteforce_Gpairs_per_s": rows * rows / ms_b / 1e6, "speedup_vs_bruteforce": ms_b / ms_c,
            "recall@1_all": r1, "recall@1_planted_half": r1p, "index_agreement_top2": r2}
     if e2e:
@@ -105,12 +128,14 @@ def run(rows=1_000_000, dim=128, reps=5, cpu_rows=2000, e2e=True):
         out["parity_bit_exact"] = bool((ci[:cpu_rows].cpu().numpy().view(np.uint64) == oi).all() and (cd[:cpu_rows].cpu().numpy() == od).all())
         if po.have_ref():
             # the reference's own CascadingHashNn: construction hashes ALL train rows and builds the tables serially
-            t0 = time.perf_counter(); po.ref_cascade(xf, yf[:1], m, n, g, seed=7); t_build = time.perf_counter() - t0
-            t0 = time.perf_counter(); ri, rd = po.ref_cascade(xf, yf, m, n, g, seed=7)[:2]; t_all = time.perf_counter() - t0
-            per_q = max(t_all - t_build, 1e-9) / cpu_rows
+            nq = min(rows, 100_000)            # enough queries for the per-query share to stand out of the construction time
+            yq = y[:nq].cpu().numpy().astype("float32") - 128
+            t0 = time.perf_counter(); po.ref_cascade(xf, yq[:1], m, n, g, seed=7); t_build = time.perf_counter() - t0
+            t0 = time.perf_counter(); ri, rd = po.ref_cascade(xf, yq, m, n, g, seed=7)[:2]; t_all = time.perf_counter() - t0
+            per_q = max(t_all - t_build, 0.0) / nq
             out["cpu_baseline"] = {"kind": "reference", "cores": "8 (CascadingHashNn.h:230 default nthread) for the re-rank; hashing / tables serial",
                                    "construction_s(hash %d train rows + build tables)" % rows: t_build,
-                                   "per_query_us": per_q * 1e6, "queries": cpu_rows,
+                                   "per_query_us": per_q * 1e6, "queries": nq, "whole_call_s(%d queries)" % nq: t_all,
                                    "whole_call_extrapolated_s(%d queries)" % rows: t_build + per_q * rows,
                                    "queries_per_s(whole call)": rows / (t_build + per_q * rows)}
         else:
