@@ -211,8 +211,20 @@ __device__ __forceinline__ void ksad_last(uint32_t (&acc)[TY][TX], int (&rs)[TY]
     }
 }
 
+// Seeds of one query tile: a warp's 32 rows' (best, second) keys from the global buffer into its shared state.
+// Deliberately NOT inlined: with the loads inline the key pointer and stride stay live across the SAD loop of a
+// kernel that sits at its 168-register cap, and the hot loop's schedule degrades (measured on the same box:
+// 523.7 vs 528.6 G pairs/s); behind a call they are fetched from the constant bank when needed.
+__device__ __noinline__ void seed_rows(const Params* __restrict__ p, unsigned long long* st, int srow) {
+  unsigned long long s1 = KEY_NONE, s2 = KEY_NONE;
+  if (srow < p->yrows) { s1 = __ldcg(p->keys + srow); s2 = __ldcg(p->keys + p->kstride + srow); }
+  st[0] = s1;
+  st[BY] = s2;
+}
+
 __global__ void __launch_bounds__(NTHREADS, 1)
-l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmy, const Params p) {
+l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmy,
+               const __grid_constant__ Params p) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int nk16 = p.nk16, NST = p.nst;
   unsigned char* ytile = smem;
@@ -300,15 +312,12 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
       // so that a launch does not pay the threshold warm-up (~2 ln N slow-path hits per query row) again.
       // A stale read only means a weaker threshold; the pair is published again through fold_key, which
       // ignores a key that is already there.
-      {
-        const int srow = yt * BY + warp * 32 + lane;
-        unsigned long long s1 = KEY_NONE, s2 = KEY_NONE;
 #ifndef SPV_K1_NO_SEED   // (A/B builds only: tools/gpu_r2_c.sh)
-        if (srow < p.yrows) { s1 = __ldcg(p.keys + srow); s2 = __ldcg(p.keys + p.kstride + srow); }
+      seed_rows(&p, st + lane, yt * BY + warp * 32 + lane);
+#else
+      st[lane] = KEY_NONE;
+      st[BY + lane] = KEY_NONE;
 #endif
-        st[lane] = s1;
-        st[BY + lane] = s2;
-      }
       __syncwarp();
 #pragma unroll
       for (int i = 0; i < TY; ++i) negthr[i] = 0u - thr_of(st[BY + ly + 4 * i]);
