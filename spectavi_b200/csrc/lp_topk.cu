@@ -478,7 +478,7 @@ cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int 
   int dev = 0, sms = 0;
   if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
   if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-  if (!is_int && k <= LP_MAX_K) {
+  if (!is_int) {
     // float32 rows: the TMA-fed kernel (lp_topk_tma.cu) when the caller's scratch admits its transposed copies
     const char* force = getenv("SPECTAVI_K1F");
     const size_t need = lp_tma_ws_bytes(xrows, yrows, dim, k, sms);

@@ -35,6 +35,7 @@ constexpr int NCT = NCW * 32;    // compute threads
 constexpr int NT = NCT + 32;     // + the producer warp
 constexpr uint32_t THR_NONE = 0xFFFFFFFFu;
 constexpr int STAGE_FLOATS = 2 * KC * TB;   // x panel then y panel, [col][row]
+constexpr int LP_TMA_MAX_K = 64;            // lists (1 KB per k) + 64 KB of parked tiles + >= 3 stages must fit 200 KB
 
 enum PMode { P_POW = 0, P_ONE = 1, P_TWO = 2, P_HALF = 3 };
 
@@ -160,7 +161,8 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
   uint32_t* thr = reinterpret_cast<uint32_t*>(ring + (size_t)nst * STAGE_FLOATS);   // [TB] k-th best distance bits
   int* cnt = reinterpret_cast<int*>(thr + TB);                                       // [TB] entries in each row's list
   unsigned long long* list = reinterpret_cast<unsigned long long*>(cnt + TB);        // [TB][k] ascending
-  unsigned long long* bars = list + (size_t)TB * k;                                  // full[nst], empty[nst]
+  float4* scratch = reinterpret_cast<float4*>(list + (size_t)TB * k);                // [NCW][16][32]: parked register tiles
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(scratch + NCW * 512);   // full[nst], empty[nst]
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nst;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -244,76 +246,102 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
       if (++stage == nst) { stage = 0; phase ^= 1; }
     }
 
-    // ---- selection, warp-local.  A warp owns 16 query rows outright (two groups of 16 lanes, 8 rows each, every
-    // lane 8 train rows), so a row's candidates all come from ONE warp and its sorted list needs no CTA-wide
-    // barrier: candidates (dist <= the row's k-th best so far) are handed, one ballot bit at a time, to the
-    // group's first lane, which inserts them into the row's list in shared memory.  Warps therefore drift apart
-    // -- one selects while the others accumulate -- instead of meeting at four barriers per train tile
-    // (measured: with CTA-wide selection and one CTA per SM this kernel was SLOWER than the register-staged one,
-    // 4.84 vs 4.59 ms at 20 k x 20 k x 132: nothing overlapped the selection phase).
+    // ---- selection, warp-local and COMPACT.  A warp owns 16 query rows outright (two groups of 16 lanes, 8 rows each,
+    // every lane 8 train rows), so a row's candidates all come from ONE warp and its sorted list needs no CTA-wide
+    // barrier: warps drift apart -- one selects while the others accumulate.  The common case costs ~80 instructions:
+    // per row the minimum of the lane's 8 distances against the row's k-th best.  Only when some lane has a hit does
+    // the warp park its accumulators in shared memory and walk the candidates in a small dynamic loop (one ballot bit
+    // at a time, the group's first lane inserting into the row's list).  (First form of this kernel: CTA-wide queue +
+    // 4 barriers per tile, slower than the register-staged kernel; second: fully unrolled per-(i, j) ballots, 2 300
+    // instructions per tile and 10 k instructions of code -- ncu: 36 % of the compute warps' time outside the FADD2
+    // loop, stall_no_instruction 15 %.)
     uint32_t thb[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) thb[i] = thr[ty * 8 + i];
-    if (t == t0 && k <= 16) {
+    const bool xin = x0 + TB <= xcnt;                    // no zero-filled train rows in this tile (CTA-uniform)
+    if (t == t0 && k <= 16 && xin) {
       // first train tile: no row has a k-th best yet; the k-th smallest of the 16 per-lane minima of a row bounds
       // its k-th distance from above
       const int hb = lane & 16;
-#pragma unroll
+#pragma unroll 1
       for (int i = 0; i < 8; ++i) {
-        uint32_t mn = THR_NONE;
+        float mf = acc[0][0];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (x0 + xrow(tx, j) < xcnt) mn = min(mn, __float_as_uint(acc[i][j]));
+        for (int ii = 0; ii < 8; ++ii)
+          if (ii == i) {
+            mf = fminf(fminf(fminf(acc[ii][0], acc[ii][1]), fminf(acc[ii][2], acc[ii][3])),
+                       fminf(fminf(acc[ii][4], acc[ii][5]), fminf(acc[ii][6], acc[ii][7])));
+          }
+        const uint32_t mn = __float_as_uint(mf);
         int rank = 0;
-#pragma unroll
+#pragma unroll 4
         for (int o = 0; o < 16; ++o) {
           const uint32_t v = __shfl_sync(0xFFFFFFFFu, mn, hb | o);
           rank += (v < mn) || (v == mn && o < tx);
         }
         const unsigned has = (__ballot_sync(0xFFFFFFFFu, rank == k - 1) >> hb) & 0xFFFFu;   // exactly one lane
         const uint32_t bound = __shfl_sync(0xFFFFFFFFu, mn, hb | (__ffs(has) - 1));
-        if (thb[i] == THR_NONE) thb[i] = bound;     // THR_NONE again when fewer than k lanes hold a valid pair
+#pragma unroll
+        for (int ii = 0; ii < 8; ++ii)
+          if (ii == i && thb[ii] == THR_NONE) thb[ii] = bound;
       }
     }
-    unsigned long long pend = 0;
+    unsigned rowhit = 0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < 8; ++i) {
+      const float m = fminf(fminf(fminf(acc[i][0], acc[i][1]), fminf(acc[i][2], acc[i][3])),
+                            fminf(fminf(acc[i][4], acc[i][5]), fminf(acc[i][6], acc[i][7])));
+      rowhit |= (unsigned)(__float_as_uint(m) <= thb[i]) << i;          // THR_NONE admits all; NaN sums never qualify
+    }
+    if (__any_sync(0xFFFFFFFFu, rowhit != 0)) {
+      // park the register tile: element e = 8 i + j of lane l at float4 slot (e / 4) * 32 + l (conflict-free)
+      float4* sc = scratch + warp * 512;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const bool c = (ty * 8 + i < ycnt) && (x0 + xrow(tx, j) < xcnt) && __float_as_uint(acc[i][j]) <= thb[i];
-        pend |= (unsigned long long)c << (i * 8 + j);
-      }
-    if (__any_sync(0xFFFFFFFFu, pend != 0)) {
+      for (int c = 0; c < 16; ++c)
+        sc[c * 32 + lane] = make_float4(acc[c >> 1][(c & 1) * 4], acc[c >> 1][(c & 1) * 4 + 1], acc[c >> 1][(c & 1) * 4 + 2],
+                                        acc[c >> 1][(c & 1) * 4 + 3]);
+      __syncwarp();
+      const float* scf = reinterpret_cast<const float*>(sc);
+      unsigned long long pend = 0;
+#pragma unroll 1
+      for (unsigned rh = rowhit; rh; rh &= rh - 1) {
+        const int i = __ffs(rh) - 1;
+        uint32_t th = thb[0];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const unsigned rm = (unsigned)(pend >> (i * 8)) & 0xFFu;
-        if (!__any_sync(0xFFFFFFFFu, rm != 0)) continue;
-#pragma unroll
+        for (int ii = 1; ii < 8; ++ii) th = (ii == i) ? thb[ii] : th;
+        if (ty * 8 + i >= ycnt) continue;
+#pragma unroll 1
         for (int j = 0; j < 8; ++j) {
-          unsigned b = __ballot_sync(0xFFFFFFFFu, (rm >> j) & 1u);
-          const unsigned long long mykey = ((unsigned long long)__float_as_uint(acc[i][j]) << 32) | (uint32_t)(x0 + xrow(tx, j));
-          while (b) {
-            const int src = __ffs(b) - 1;
-            b &= b - 1;
-            const unsigned long long key = __shfl_sync(0xFFFFFFFFu, mykey, src);
-            if (lane == (src & 16)) {                 // the first lane of the candidate's 16-lane group owns the row's list
-              const int row = (warp * 2 + (src >> 4)) * 8 + i;
-              unsigned long long* L = list + (size_t)row * k;
-              int m = cnt[row];
-              bool take = true;
-              if (m == k) {
-                if (key >= L[k - 1]) take = false;    // beaten meanwhile by an earlier candidate of this tile
-                else --m;                             // drop the current k-th
-              }
-              if (take) {
-                int pos = m;
-                while (pos > 0 && L[pos - 1] > key) { L[pos] = L[pos - 1]; --pos; }
-                L[pos] = key;
-                ++m;
-                cnt[row] = m;
-                thr[row] = (m == k) ? (uint32_t)(L[k - 1] >> 32) : THR_NONE;
-              }
-            }
+          const int e = i * 8 + j;
+          const uint32_t v = __float_as_uint(scf[((e >> 2) * 32 + lane) * 4 + (e & 3)]);
+          if (v <= th && x0 + xrow(tx, j) < xcnt) pend |= 1ull << e;
+        }
+      }
+#pragma unroll 1
+      for (;;) {
+        const unsigned b = __ballot_sync(0xFFFFFFFFu, pend != 0);
+        if (!b) break;
+        const int src = __ffs(b) - 1;
+        const int e = __shfl_sync(0xFFFFFFFFu, __ffsll((long long)pend) - 1, src);
+        if (lane == src) pend &= pend - 1;
+        if (lane == (src & 16)) {                       // the first lane of the candidate's 16-lane group owns the row's list
+          const uint32_t v = __float_as_uint(scf[((e >> 2) * 32 + src) * 4 + (e & 3)]);
+          const unsigned long long key = ((unsigned long long)v << 32) | (uint32_t)(x0 + xrow(src & 15, e & 7));
+          const int row = (warp * 2 + (src >> 4)) * 8 + (e >> 3);
+          unsigned long long* L = list + (size_t)row * k;
+          int m = cnt[row];
+          bool take = true;
+          if (m == k) {
+            if (key >= L[k - 1]) take = false;          // beaten meanwhile by an earlier candidate of this tile
+            else --m;                                   // drop the current k-th
+          }
+          if (take) {
+            int pos = m;
+            while (pos > 0 && L[pos - 1] > key) { L[pos] = L[pos - 1]; --pos; }
+            L[pos] = key;
+            ++m;
+            cnt[row] = m;
+            thr[row] = (m == k) ? (uint32_t)(L[k - 1] >> 32) : THR_NONE;
           }
         }
       }
@@ -354,7 +382,7 @@ int pick_splits_tma(int ny_tiles, int nxt, int sms, size_t rows_times_k) {
   return best;
 }
 
-size_t fixed_smem(int k) { return (size_t)TB * 4 * 2 + (size_t)TB * k * 8; }
+size_t fixed_smem(int k) { return (size_t)TB * 4 * 2 + (size_t)TB * k * 8 + (size_t)NCW * 512 * 16; }
 
 template <int PM>
 cudaError_t launch(const CUtensorMap& tmx, const CUtensorMap& tmy, const TmaParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
@@ -372,7 +400,7 @@ int lp_tma_splits(int xrows, int yrows, int k, int sms) {
 }
 
 size_t lp_tma_ws_bytes(int xrows, int yrows, int dim, int k, int sms) {
-  if (k < 1 || k > LP_MAX_K || dim < 1) return 0;
+  if (k < 1 || k > LP_TMA_MAX_K || dim < 1) return 0;   // larger lists leave no room for the ring: register-staged kernel
   const size_t lists = (size_t)lp_tma_splits(xrows, yrows, k, sms) * (size_t)(yrows > 0 ? yrows : 0) * k * sizeof(unsigned long long);
   return al256(lists) + al256((size_t)dim * pitch_of(xrows) * 4) + al256((size_t)dim * pitch_of(yrows) * 4) + 256;
 }
