@@ -302,20 +302,23 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
                                         acc[c >> 1][(c & 1) * 4 + 3]);
       __syncwarp();
       const float* scf = reinterpret_cast<const float*>(sc);
-      unsigned long long pend = 0;
-#pragma unroll 1
-      for (unsigned rh = rowhit; rh; rh &= rh - 1) {
-        const int i = __ffs(rh) - 1;
-        uint32_t th = thb[0];
+      // which of the lane's pairs qualify: per ROW a warp-uniform test first (typically one or two rows of a tile have a
+      // hit anywhere in the warp), then 8 register compares; zero-filled train rows only exist in the last tile
+      unsigned jvalid = 0xFFu;
+      if (!xin) {
+        jvalid = 0;
 #pragma unroll
-        for (int ii = 1; ii < 8; ++ii) th = (ii == i) ? thb[ii] : th;
-        if (ty * 8 + i >= ycnt) continue;
-#pragma unroll 1
-        for (int j = 0; j < 8; ++j) {
-          const int e = i * 8 + j;
-          const uint32_t v = __float_as_uint(scf[((e >> 2) * 32 + lane) * 4 + (e & 3)]);
-          if (v <= th && x0 + xrow(tx, j) < xcnt) pend |= 1ull << e;
-        }
+        for (int j = 0; j < 8; ++j) jvalid |= (unsigned)(x0 + xrow(tx, j) < xcnt) << j;
+      }
+      unsigned long long pend = 0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (!__any_sync(0xFFFFFFFFu, (rowhit >> i) & 1u)) continue;
+        unsigned mk = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) mk |= (unsigned)(__float_as_uint(acc[i][j]) <= thb[i]) << j;
+        if (ty * 8 + i >= ycnt) mk = 0;
+        pend |= (unsigned long long)(mk & jvalid) << (8 * i);
       }
 #pragma unroll 1
       for (;;) {
