@@ -150,6 +150,7 @@ struct TmaParams {
   double p;
   int nxt, splits, nst;
   unsigned long long* partial;   // [splits][yrows][k]
+  uint32_t* gthr;                // [yrows] smallest k-th-best distance (bits) any train split has reached so far
 };
 
 template <int PM>
@@ -160,7 +161,8 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
   float* ring = reinterpret_cast<float*>(smem_raw);                                  // [nst][x panel | y panel][KC][TB]
   uint32_t* thr = reinterpret_cast<uint32_t*>(ring + (size_t)nst * STAGE_FLOATS);   // [TB] k-th best distance bits
   int* cnt = reinterpret_cast<int*>(thr + TB);                                       // [TB] entries in each row's list
-  unsigned long long* list = reinterpret_cast<unsigned long long*>(cnt + TB);        // [TB][k] ascending
+  uint32_t* teff = reinterpret_cast<uint32_t*>(cnt + TB);                            // [TB] min(own, shared) threshold of the tile
+  unsigned long long* list = reinterpret_cast<unsigned long long*>(teff + TB);       // [TB][k] ascending
   float4* scratch = reinterpret_cast<float4*>(list + (size_t)TB * k);                // [NCW][16][32]: parked register tiles
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(scratch + NCW * 512);   // full[nst], empty[nst]
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nst;
@@ -210,12 +212,21 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
     for (int i = 0; i < 8; ++i)
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    // The train set is split over gridDim.y CTAs per query tile, each scanning its share cold: without help every
+    // split re-pays the threshold warm-up (ncu: ~8 candidates per warp and tile at 10 splits where one scan would
+    // produce ~1).  So the splits share, per query row, the smallest k-th-best distance any of them has reached
+    // (a candidate farther than that cannot be among the final k; ties go through and the merge compares whole keys).
+    // The load is issued here and consumed after the column loop.
+    uint32_t gth = THR_NONE;
+    if (lane < 16 && warp * 16 + lane < ycnt) gth = __ldcg(P.gthr + y0 + warp * 16 + lane);
 
     for (int pn = 0; pn < npanels; ++pn) {
       mbar_wait(bar_full + 8 * stage, phase);
       const float* xs = ring + (size_t)stage * STAGE_FLOATS;
       const float* ys = xs + KC * TB;
-      const int kc = min(KC, dim - pn * KC);
+      // columns past dim are TMA zero fill: |0 - 0|, 0 * 0 and sqrtf(0) add +0.0, which changes nothing, so the trip
+      // count stays a constant; only pow(0, p) (1 at p == 0, inf below) must not see them
+      const int kc = (PM == P_POW) ? min(KC, dim - pn * KC) : KC;
 #pragma unroll 4
       for (int c = 0; c < kc; ++c) {
         float ya[8], xb[8];
@@ -255,9 +266,11 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
     // 4 barriers per tile, slower than the register-staged kernel; second: fully unrolled per-(i, j) ballots, 2 300
     // instructions per tile and 10 k instructions of code -- ncu: 36 % of the compute warps' time outside the FADD2
     // loop, stall_no_instruction 15 %.)
+    if (lane < 16) teff[warp * 16 + lane] = min(thr[warp * 16 + lane], gth);
+    __syncwarp();
     uint32_t thb[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) thb[i] = thr[ty * 8 + i];
+    for (int i = 0; i < 8; ++i) thb[i] = teff[ty * 8 + i];
     const bool xin = x0 + TB <= xcnt;                    // no zero-filled train rows in this tile (CTA-uniform)
     if (t == t0 && k <= 16 && xin) {
       // first train tile: no row has a k-th best yet; the k-th smallest of the 16 per-lane minima of a row bounds
@@ -344,7 +357,11 @@ lp_topk_tma_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constan
             L[pos] = key;
             ++m;
             cnt[row] = m;
-            thr[row] = (m == k) ? (uint32_t)(L[k - 1] >> 32) : THR_NONE;
+            if (m == k) {
+              const uint32_t kth = (uint32_t)(L[k - 1] >> 32);
+              thr[row] = kth;
+              if (row < ycnt) atomicMin(P.gthr + y0 + row, kth);   // tell the other train splits
+            }
           }
         }
       }
@@ -385,7 +402,7 @@ int pick_splits_tma(int ny_tiles, int nxt, int sms, size_t rows_times_k) {
   return best;
 }
 
-size_t fixed_smem(int k) { return (size_t)TB * 4 * 2 + (size_t)TB * k * 8 + (size_t)NCW * 512 * 16; }
+size_t fixed_smem(int k) { return (size_t)TB * 4 * 3 + (size_t)TB * k * 8 + (size_t)NCW * 512 * 16; }
 
 template <int PM>
 cudaError_t launch(const CUtensorMap& tmx, const CUtensorMap& tmy, const TmaParams& P, dim3 grid, size_t smem, cudaStream_t stream) {
@@ -405,7 +422,8 @@ int lp_tma_splits(int xrows, int yrows, int k, int sms) {
 size_t lp_tma_ws_bytes(int xrows, int yrows, int dim, int k, int sms) {
   if (k < 1 || k > LP_TMA_MAX_K || dim < 1) return 0;   // larger lists leave no room for the ring: register-staged kernel
   const size_t lists = (size_t)lp_tma_splits(xrows, yrows, k, sms) * (size_t)(yrows > 0 ? yrows : 0) * k * sizeof(unsigned long long);
-  return al256(lists) + al256((size_t)dim * pitch_of(xrows) * 4) + al256((size_t)dim * pitch_of(yrows) * 4) + 256;
+  return al256(lists) + al256((size_t)dim * pitch_of(xrows) * 4) + al256((size_t)dim * pitch_of(yrows) * 4) +
+         al256((size_t)(yrows > 0 ? yrows : 1) * 4) + 256;
 }
 
 // didx / ddist must already hold the caller's zeros (lp_topk does that); *partial_out / *splits_out tell the caller
@@ -421,18 +439,22 @@ cudaError_t lp_topk_tma(const float* dx, const float* dy, int xrows, int yrows, 
   float* xT = reinterpret_cast<float*>(w);
   w += al256((size_t)dim * xp * 4);
   float* yT = reinterpret_cast<float*>(w);
+  w += al256((size_t)dim * yp * 4);
+  uint32_t* gthr = reinterpret_cast<uint32_t*>(w);
+  cudaError_t e = cudaMemsetAsync(gthr, 0xFF, (size_t)yrows * 4, stream);
+  if (e != cudaSuccess) return e;
   const dim3 tb(32, 8);
   transpose_f32_kernel<<<dim3((xrows + 31) / 32, (dim + 31) / 32), tb, 0, stream>>>(dx, xrows, dim, xT, xp);
   transpose_f32_kernel<<<dim3((yrows + 31) / 32, (dim + 31) / 32), tb, 0, stream>>>(dy, yrows, dim, yT, yp);
   count_launch(2);
-  cudaError_t e = cudaGetLastError();
+  e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   CUtensorMap tmx, tmy;
   if (!make_f32_panel_map(&tmx, xT, xrows, dim, xp, TB, KC) || !make_f32_panel_map(&tmy, yT, yrows, dim, yp, TB, KC))
     return cudaErrorInvalidValue;
   TmaParams P;
   P.xrows = xrows; P.yrows = yrows; P.dim = dim; P.k = k; P.p = p;
-  P.nxt = (xrows + TB - 1) / TB; P.splits = splits; P.partial = partial;
+  P.nxt = (xrows + TB - 1) / TB; P.splits = splits; P.partial = partial; P.gthr = gthr;
   const size_t fixed = fixed_smem(k) + 2 * 8 * 16 + 1024, stage = (size_t)STAGE_FLOATS * 4;
   int nst = (int)(((size_t)200 * 1024 - fixed) / stage);
   nst = nst > 10 ? 10 : nst;
