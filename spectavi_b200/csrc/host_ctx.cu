@@ -66,6 +66,7 @@ struct Gpu {
   cudaStream_t stream = nullptr;
   Lane lane[4];
   bool lanes_ready = false;
+  cudaEvent_t ev[16] = {};      // scratch events (per-chunk completion of the final pass)
   Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws, rws, sel;
   PinBuf res;
 };
@@ -191,6 +192,7 @@ void lanes_init(const char* fn, Gpu& D) {
     }
     CU(fn, cudaEventCreateWithFlags(&L.ready, cudaEventDisableTiming));
   }
+  for (cudaEvent_t& e : D.ev) CU(fn, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   D.lanes_ready = true;
 }
 
@@ -211,6 +213,8 @@ void lane_upload(const char* fn, Lane& L, void* dst, const void* src, size_t byt
   }
   CU(fn, cudaEventRecord(L.ready, L.copy));
 }
+
+void copy_out(void* dst, const void* src, size_t bytes);
 
 // Piece sizes of a streamed matrix: the first piece is small, so that compute starts after a fraction of a
 // millisecond of upload, and the pieces double up to `cap` rows so that the launch count stays small.
@@ -233,7 +237,12 @@ std::vector<int> piece_rows(int rows, int first, int cap, int align) {
 // each matched against the first, small train piece as soon as it has landed; then the remaining train pieces,
 // each against all query rows.  K1 folds into one key buffer across launches (xoffset) and seeds its thresholds
 // from it (l1_top2.cu), so the chunking costs no extra slow-path work.  Nothing is synchronised here.
-void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* y, int x0, int xn, int yrows, int dim) {
+// With hidx / hdist (single-GPU calls) the shard also delivers: the LAST pass over a slice of query rows makes that
+// slice final, so the last train piece is matched slice by slice (up to 4), each followed by keys_finalize on the
+// slice and a DMA into pinned memory on a second stream; the host copies slice c out while slice c + 1 computes, and
+// only the last slice's delivery is exposed (traced on C3: finalize + D2H + copy-out of all 4.8 MB cost 1.4 ms behind K1).
+void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* y, int x0, int xn, int yrows, int dim,
+                       uint64_t* hidx = nullptr, int32_t* hdist = nullptr) {
   const Trace tr;
   CU(fn, cudaSetDevice(D.dev));
   lanes_init(fn, D);
@@ -263,12 +272,55 @@ void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* 
     yo += rows;
   }
   int xo = xp[0];
+  const size_t last = xp.size() - 1;
+  const bool deliver = hidx != nullptr && last >= 1;      // (one train piece only: the caller finalises the whole buffer)
   for (size_t i = 1; i < xp.size(); ++i) {
     lane_upload(fn, L, dx + (size_t)xo * dim, x + (size_t)(x0 + xo) * dim, (size_t)xp[i] * dim);
     CU(fn, cudaStreamWaitEvent(D.stream, L.ready, 0));
-    CU(fn, l1_top2_u8(dx + (size_t)xo * dim, dy, xp[i], yrows, dim, (uint32_t)(x0 + xo), dk, D.stream, yrows));
-    tr("x piece queued + K1 launched", xp[i]);
+    if (!(deliver && i == last)) {
+      CU(fn, l1_top2_u8(dx + (size_t)xo * dim, dy, xp[i], yrows, dim, (uint32_t)(x0 + xo), dk, D.stream, yrows));
+      tr("x piece queued + K1 launched", xp[i]);
+      xo += xp[i];
+      continue;
+    }
+    // the final pass, slice by slice
+    int nq = yrows / 8192;
+    nq = nq < 1 ? 1 : (nq > 4 ? 4 : nq);
+    const int per = ((yrows + nq - 1) / nq + 255) / 256 * 256;
+    const size_t ib = (size_t)yrows * 2 * sizeof(uint64_t), db = (size_t)yrows * 2 * sizeof(int32_t), doff = (ib + 255) & ~(size_t)255;
+    CU(fn, D.oidx.ensure(ib));
+    CU(fn, D.odist.ensure(db));
+    CU(fn, D.res.ensure(doff + db));
+    char* pin = static_cast<char*>(D.res.p);
+    cudaStream_t down = D.lane[1].copy;
+    int nslice = 0, y0s[4], yns[4];
+    for (int c0 = 0; c0 < yrows; c0 += per) {
+      const int rows = yrows - c0 < per ? yrows - c0 : per;
+      CU(fn, l1_top2_u8(dx + (size_t)xo * dim, dy + (size_t)c0 * dim, xp[i], rows, dim, (uint32_t)(x0 + xo), dk + c0, D.stream, yrows));
+      CU(fn, keys_finalize_i32(dk + c0, rows, 2, (uint64_t*)D.oidx.p + (size_t)c0 * 2, (int32_t*)D.odist.p + (size_t)c0 * 2, D.stream, yrows));
+      CU(fn, cudaEventRecord(D.ev[nslice], D.stream));
+      CU(fn, cudaStreamWaitEvent(down, D.ev[nslice], 0));
+      CU(fn, cudaMemcpyAsync(pin + (size_t)c0 * 16, (char*)D.oidx.p + (size_t)c0 * 16, (size_t)rows * 16, cudaMemcpyDeviceToHost, down));
+      CU(fn, cudaMemcpyAsync(pin + doff + (size_t)c0 * 8, (char*)D.odist.p + (size_t)c0 * 8, (size_t)rows * 8, cudaMemcpyDeviceToHost, down));
+      CU(fn, cudaEventRecord(D.ev[8 + nslice], down));
+      y0s[nslice] = c0; yns[nslice] = rows;
+      ++nslice;
+    }
+    tr("final pass queued in slices", nslice);
+    for (int c = 0; c < nslice; ++c) {
+      CU(fn, cudaEventSynchronize(D.ev[8 + c]));
+      copy_out((char*)hidx + (size_t)y0s[c] * 16, pin + (size_t)y0s[c] * 16, (size_t)yns[c] * 16);
+      copy_out((char*)hdist + (size_t)y0s[c] * 8, pin + doff + (size_t)y0s[c] * 8, (size_t)yns[c] * 8);
+    }
+    CU(fn, cudaStreamSynchronize(D.stream));
+    tr("results on the host (sliced)");
     xo += xp[i];
+  }
+  if (hidx && !deliver) {
+    // a single train piece: finalise the whole buffer behind the query pieces
+    CU(fn, D.oidx.ensure((size_t)yrows * 2 * sizeof(uint64_t)));
+    CU(fn, D.odist.ensure((size_t)yrows * 2 * sizeof(int32_t)));
+    CU(fn, keys_finalize_i32(dk, yrows, 2, (uint64_t*)D.oidx.p, (int32_t*)D.odist.p, D.stream));
   }
 }
 
@@ -435,12 +487,20 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
   const int per = (xrows + G - 1) / G;   // train rows per GPU
   const char* fn = fn_;
   // every GPU streams its own train shard and its own copy of the query rows over its own PCIe link
+  const bool self_deliver = G == 1 && !ms && xrows > 0;
   per_gpu(c, [&](int g) {
     const int x0 = (long long)g * per < xrows ? g * per : xrows;
     const int xn = (x0 + per <= xrows) ? per : xrows - x0;
-    l1k2_stream_shard(fn, c.gpus[g], x, y, x0, xn, yrows, dim);
+    l1k2_stream_shard(fn, c.gpus[g], x, y, x0, xn, yrows, dim, self_deliver ? idx : nullptr, self_deliver ? dist : nullptr);
   });
   const Trace tr;
+  if (self_deliver) {
+    Gpu& R0 = c.gpus[0];
+    const std::vector<int> xp = piece_rows(xrows, 8192, 65536, 64);
+    if (xp.size() >= 2) return;                       // delivered slice by slice inside the shard
+    fetch_results(fn_, c, R0, idx, R0.oidx.p, (size_t)yrows * 2 * sizeof(uint64_t), dist, R0.odist.p, (size_t)yrows * 2 * sizeof(int32_t));
+    return;
+  }
   merge_shards(fn_, c, yrows);
   if (ms) {
     deliver_matches(*ms, yrows, false);

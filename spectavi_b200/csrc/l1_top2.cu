@@ -495,7 +495,7 @@ __global__ void keys_merge_kernel(unsigned long long* __restrict__ dst, const un
 
 template <typename D>
 __global__ void keys_finalize_kernel(const unsigned long long* __restrict__ keys, int yrows, int kcols,
-                                     uint64_t* __restrict__ idx, D* __restrict__ dist) {
+                                     uint64_t* __restrict__ idx, D* __restrict__ dist, long long kstride) {
   // BruteForceNnL1K2.h:99-103 sentinels: idx (size_t)-1, dist INT_MAX; the cascade
   // reports (float)INT_MAX (CascadingHashNn.h:244).  Columns >= 2 (k > 2 on the
   // cascade ABI, Spectavi.cpp:329-334) are left as the caller's zeros.
@@ -504,7 +504,7 @@ __global__ void keys_finalize_kernel(const unsigned long long* __restrict__ keys
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
     if (r >= kcols) break;
-    const unsigned long long k = keys[(size_t)r * yrows + row];
+    const unsigned long long k = keys[(size_t)r * kstride + row];
     const bool none = (k == KEY_NONE);
     idx[(size_t)row * kcols + r] = none ? ~0ull : (k & 0xFFFFFFFFull);
     dist[(size_t)row * kcols + r] = none ? (D)2147483647 : (D)(int32_t)(k >> 32);
@@ -600,9 +600,9 @@ cudaError_t keys_merge(unsigned long long* dst, const unsigned long long* src, i
 }
 
 cudaError_t keys_finalize_i32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx, int32_t* dist,
-                              cudaStream_t stream) {
+                              cudaStream_t stream, long long kstride) {
   if (yrows <= 0) return cudaSuccess;
-  keys_finalize_kernel<int32_t><<<(yrows + 255) / 256, 256, 0, stream>>>(keys, yrows, kcols, idx, dist);
+  keys_finalize_kernel<int32_t><<<(yrows + 255) / 256, 256, 0, stream>>>(keys, yrows, kcols, idx, dist, kstride > 0 ? kstride : yrows);
   count_launch();
   return cudaGetLastError();
 }
@@ -610,7 +610,7 @@ cudaError_t keys_finalize_i32(const unsigned long long* keys, int yrows, int kco
 cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx, float* dist,
                               cudaStream_t stream) {
   if (yrows <= 0) return cudaSuccess;
-  keys_finalize_kernel<float><<<(yrows + 255) / 256, 256, 0, stream>>>(keys, yrows, kcols, idx, dist);
+  keys_finalize_kernel<float><<<(yrows + 255) / 256, 256, 0, stream>>>(keys, yrows, kcols, idx, dist, yrows);
   count_launch();
   return cudaGetLastError();
 }

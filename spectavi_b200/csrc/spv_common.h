@@ -39,8 +39,9 @@ cudaError_t keys_reset(unsigned long long* keys, int yrows, cudaStream_t stream)
 cudaError_t keys_merge(unsigned long long* dst, const unsigned long long* src, int nsrc, int yrows,
                        cudaStream_t stream);
 // keys -> reference output arrays (row-major yrows x 2): size_t idx, int32 dist
+// (kstride as in l1_top2_u8: keys / idx / dist may address a slice of the query rows of a larger key buffer)
 cudaError_t keys_finalize_i32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx,
-                              int32_t* dist, cudaStream_t stream);
+                              int32_t* dist, cudaStream_t stream, long long kstride = 0);
 // same but distances as float (CascadingHashNn.h:244 casts int -> float)
 cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kcols, uint64_t* idx,
                               float* dist, cudaStream_t stream);
