@@ -6,6 +6,7 @@
 #include <dlfcn.h>
 #include <nccl.h>   // types only; the library is dlopen()ed when SPECTAVI_GPUS > 1
 
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
@@ -41,7 +42,7 @@ struct PinBuf {
     if (p) cudaFreeHost(p);
     p = nullptr; cap = 0;
     const size_t want = n + n / 8 + 4096;
-    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocPortable);
     if (e == cudaSuccess) cap = want;
     return e;
   }
@@ -87,8 +88,24 @@ struct Nccl {
 // re-entrant (no globals), so concurrent callers must not serialise on one set of buffers: single-GPU calls take a
 // context from a pool (a new one is made when all are busy); the multi-GPU layout (SPECTAVI_GPUS > 1) has one
 // context, because its NCCL communicators admit one collective sequence at a time.
+struct SpinBarrier {               // the per-GPU host threads of one call meet here (short waits, dedicated threads)
+  std::atomic<int> count{0}, sense{0};
+  int n = 1;
+  void wait() {
+    const int s = sense.load(std::memory_order_acquire);
+    if (count.fetch_add(1, std::memory_order_acq_rel) + 1 == n) {
+      count.store(0, std::memory_order_relaxed);
+      sense.store(s ^ 1, std::memory_order_release);
+    } else {
+      while (sense.load(std::memory_order_acquire) == s) std::this_thread::yield();
+    }
+  }
+};
+
 struct Ctx {
   std::vector<Gpu> gpus;
+  PinBuf ypin;                     // multi-GPU: the query rows staged ONCE (portable pinned memory), DMA'd by every GPU
+  SpinBarrier bar;
 };
 
 namespace {
@@ -241,8 +258,13 @@ std::vector<int> piece_rows(int rows, int first, int cap, int align) {
 // slice final, so the last train piece is matched slice by slice (up to 4), each followed by keys_finalize on the
 // slice and a DMA into pinned memory on a second stream; the host copies slice c out while slice c + 1 computes, and
 // only the last slice's delivery is exposed (traced on C3: finalize + D2H + copy-out of all 4.8 MB cost 1.4 ms behind K1).
+// Multi-GPU (coop != nullptr): the query rows are identical for every GPU, so the G host threads stage each query
+// piece TOGETHER into one portable pinned buffer (each copies 1 / G of it), meet at a barrier, and every GPU then
+// DMAs the piece from there -- the pageable -> pinned memcpy, the slow half of the path, is done once instead of G
+// times (measured at 8 GPUs with per-GPU staging: 8 x 128 MB of memcpy starved the GPUs for ~9 ms of a 238 ms call).
+struct Coop { Ctx* c; int g, G; };
 void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* y, int x0, int xn, int yrows, int dim,
-                       uint64_t* hidx = nullptr, int32_t* hdist = nullptr) {
+                       uint64_t* hidx = nullptr, int32_t* hdist = nullptr, const Coop* coop = nullptr) {
   const Trace tr;
   CU(fn, cudaSetDevice(D.dev));
   lanes_init(fn, D);
@@ -251,26 +273,40 @@ void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* 
   CU(fn, D.y.ensure(ybytes));
   CU(fn, D.keys.ensure(kbytes));
   CU(fn, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
-  if (xn <= 0) return;
-  CU(fn, D.x.ensure((size_t)xn * dim));
+  if (xn <= 0 && !coop) return;
+  if (xn > 0) CU(fn, D.x.ensure((size_t)xn * dim));
   Lane& L = D.lane[0];
   // first train piece sized so that matching it against all query rows takes about as long as uploading them
   // (x0 * yrows * dim / 4 sad-ops at ~17 T/s  vs  yrows * dim bytes at ~10 GB/s  =>  ~7 k rows, any shape)
-  const std::vector<int> xp = piece_rows(xn, 8192, 65536, 64), yp = piece_rows(yrows, 8192, 131072, 256);
+  const std::vector<int> xp = piece_rows(xn > 0 ? xn : 1, 8192, 65536, 64), yp = piece_rows(yrows, 8192, 131072, 256);
   uint8_t* dx = (uint8_t*)D.x.p;
   uint8_t* dy = (uint8_t*)D.y.p;
   unsigned long long* dk = (unsigned long long*)D.keys.p;
   tr("buffers ready");
-  lane_upload(fn, L, dx, x + (size_t)x0 * dim, (size_t)xp[0] * dim);
+  if (xn > 0) lane_upload(fn, L, dx, x + (size_t)x0 * dim, (size_t)xp[0] * dim);
   tr("x piece queued", xp[0]);
   int yo = 0;
   for (int rows : yp) {
-    lane_upload(fn, L, dy + (size_t)yo * dim, y + (size_t)yo * dim, (size_t)rows * dim);
-    CU(fn, cudaStreamWaitEvent(D.stream, L.ready, 0));
-    CU(fn, l1_top2_u8(dx, dy + (size_t)yo * dim, xp[0], rows, dim, (uint32_t)x0, dk + yo, D.stream, yrows));
+    if (coop) {
+      uint8_t* ypin = static_cast<uint8_t*>(coop->c->ypin.p);
+      const size_t r0 = (size_t)rows * coop->g / coop->G, r1 = (size_t)rows * (coop->g + 1) / coop->G;
+      memcpy(ypin + ((size_t)yo + r0) * dim, y + ((size_t)yo + r0) * dim, (r1 - r0) * dim);
+      coop->c->bar.wait();                               // the whole piece is in pinned memory
+      if (xn > 0) {
+        CU(fn, cudaMemcpyAsync(dy + (size_t)yo * dim, ypin + (size_t)yo * dim, (size_t)rows * dim, cudaMemcpyHostToDevice, L.copy));
+        CU(fn, cudaEventRecord(L.ready, L.copy));
+      }
+    } else {
+      lane_upload(fn, L, dy + (size_t)yo * dim, y + (size_t)yo * dim, (size_t)rows * dim);
+    }
+    if (xn > 0) {
+      CU(fn, cudaStreamWaitEvent(D.stream, L.ready, 0));
+      CU(fn, l1_top2_u8(dx, dy + (size_t)yo * dim, xp[0], rows, dim, (uint32_t)x0, dk + yo, D.stream, yrows));
+    }
     tr("y piece queued + K1 launched", rows);
     yo += rows;
   }
+  if (xn <= 0) return;
   int xo = xp[0];
   const size_t last = xp.size() - 1;
   const bool deliver = hidx != nullptr && last >= 1;      // (one train piece only: the caller finalises the whole buffer)
@@ -488,10 +524,17 @@ void HostCall::l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, in
   const char* fn = fn_;
   // every GPU streams its own train shard and its own copy of the query rows over its own PCIe link
   const bool self_deliver = G == 1 && !ms && xrows > 0;
+  if (G > 1) {
+    CU(fn_, cudaSetDevice(c.gpus[0].dev));
+    CU(fn_, c.ypin.ensure((size_t)yrows * dim));
+    c.bar.n = G;
+  }
   per_gpu(c, [&](int g) {
     const int x0 = (long long)g * per < xrows ? g * per : xrows;
     const int xn = (x0 + per <= xrows) ? per : xrows - x0;
-    l1k2_stream_shard(fn, c.gpus[g], x, y, x0, xn, yrows, dim, self_deliver ? idx : nullptr, self_deliver ? dist : nullptr);
+    const Coop coop = {&c, g, G};
+    l1k2_stream_shard(fn, c.gpus[g], x, y, x0, xn, yrows, dim, self_deliver ? idx : nullptr, self_deliver ? dist : nullptr,
+                      G > 1 ? &coop : nullptr);
   });
   const Trace tr;
   if (self_deliver) {

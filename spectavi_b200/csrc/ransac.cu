@@ -175,10 +175,15 @@ __device__ __forceinline__ void transpose3(const double (&a)[9], double (&o)[9])
 
 // per hypothesis: gate + the four candidate cameras.  cams[h][c][12] row-major 3 x 4, aux[h][c] = {sign det M, |m|^2}
 // (DltTriangulator.h:28-34), valid[h] = 0 when the singular-value-ratio gate rejects F (RansacFitter.h:50-53).
+// Gated-in hypotheses are appended to vlist (order irrelevant) so that the scoring kernel only ever sees real work:
+// with seven-point draws from matches that hold outliers, most candidates fail the gate (bench: 157 of 4 001).
 __global__ void ransac_setup_kernel(const double* __restrict__ F, int nF, double sv_ratio_allowed, double* __restrict__ cams,
-                                    double* __restrict__ aux, int* __restrict__ valid) {
+                                    double* __restrict__ aux, int* __restrict__ valid, int* __restrict__ counts,
+                                    int* __restrict__ vlist, int* __restrict__ nvalid) {
   const int h = blockIdx.x * blockDim.x + threadIdx.x;
   if (h >= nF) return;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) counts[h * 4 + c] = 0;
   double a[9], sv[3], u[9], v[9];
 #pragma unroll
   for (int i = 0; i < 9; ++i) a[i] = F[(size_t)9 * h + i];
@@ -186,6 +191,7 @@ __global__ void ransac_setup_kernel(const double* __restrict__ F, int nF, double
   const double ratio = fabs(sv[0] - sv[1]) / (fabs(sv[0] + sv[1]) / 2.);
   if (ratio > sv_ratio_allowed) { valid[h] = 0; return; }   // also false for NaN, like the reference's comparison
   valid[h] = 1;
+  vlist[atomicAdd(nvalid, 1)] = h;
   // E = U * diag(1, 1, 0) * V^T
   double ud[9], vt[9], E[9];
 #pragma unroll
@@ -218,27 +224,28 @@ __global__ void ransac_setup_kernel(const double* __restrict__ F, int nF, double
 }
 
 constexpr int RS_THREADS = 128;
+constexpr int RS_CHUNK = 4 * RS_THREADS;   // matches per work item
 
-// one block per (hypothesis, camera): every thread takes matches ix = tid, tid + 128, ...
-// counts[h][c], masks[(h * 4 + c) * W + word] (bit = match & 31)
+// Persistent blocks over work items (gated-in hypothesis, camera, chunk of 512 matches): every thread takes 4 matches
+// of the chunk.  counts[h][c] (zeroed by the setup kernel) collects the chunk counts; masks[(h * 4 + c) * W + word]
+// (bit = match & 31) are written whole words at a time, one warp per word.
 __global__ void __launch_bounds__(RS_THREADS) ransac_score_kernel(const double* __restrict__ cams, const double* __restrict__ aux,
-                                                                  const int* __restrict__ valid, const double* __restrict__ x0,
-                                                                  const double* __restrict__ x1, int npt, double err_allowed,
-                                                                  int* __restrict__ counts, uint32_t* __restrict__ masks, int W) {
-  const int hc = blockIdx.x, h = hc >> 2;
-  __shared__ int s_count;
-  if (threadIdx.x == 0) s_count = 0;
-  __syncthreads();
-  if (!valid[h]) {
-    if (threadIdx.x == 0) counts[hc] = 0;
-    return;
-  }
+                                                                  const int* __restrict__ vlist, const int* __restrict__ nvalid,
+                                                                  const double* __restrict__ x0, const double* __restrict__ x1,
+                                                                  int npt, double err_allowed, int* __restrict__ counts,
+                                                                  uint32_t* __restrict__ masks, int W) {
+  const int nchunk = (npt + RS_CHUNK - 1) / RS_CHUNK;
+  const long long total = (long long)(*nvalid) * 4 * nchunk;
+  for (long long item = blockIdx.x; item < total; item += gridDim.x) {
+  const int chunk = (int)(item % nchunk);
+  const int hc = vlist[item / nchunk / 4] * 4 + (int)((item / nchunk) % 4);
   double P[12];
 #pragma unroll
   for (int i = 0; i < 12; ++i) P[i] = cams[(size_t)hc * 12 + i];
   const double sign1 = aux[(size_t)hc * 2], norm1 = aux[(size_t)hc * 2 + 1];
   int mine = 0;
-  for (int base = 0; base < npt; base += RS_THREADS) {
+  const int cend = min(npt, (chunk + 1) * RS_CHUNK);
+  for (int base = chunk * RS_CHUNK; base < cend; base += RS_THREADS) {
     const int ix = base + threadIdx.x;
     bool inlier = false;
     if (ix < npt) {
@@ -274,9 +281,8 @@ __global__ void __launch_bounds__(RS_THREADS) ransac_score_kernel(const double* 
       mine += __popc(bal);
     }
   }
-  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&s_count, mine);
-  __syncthreads();
-  if (threadIdx.x == 0) counts[hc] = s_count;
+  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(counts + hc, mine);
+  }
 }
 
 // per hypothesis: the reference's camera choice (RansacFitter.h:59-80): cameras in order, a camera wins when
@@ -316,7 +322,7 @@ size_t ransac_ws_bytes(int nF, int npt) {
   if (nF < 0 || npt < 0) return 0;
   const size_t W = ((size_t)npt + 31) / 32;
   return al256((size_t)nF * 4 * 12 * 8) + al256((size_t)nF * 4 * 2 * 8) + al256((size_t)nF * 4) + al256((size_t)nF * 4 * 4) +
-         al256((size_t)nF * 4 * W * 4) + 256;
+         al256((size_t)nF * 4 + 16) + al256((size_t)nF * 4 * W * 4) + 256;
 }
 
 cudaError_t ransac_score(const double* dF, int nF, const double* dx0, const double* dx1, int npt, double required_percent_inliers,
@@ -331,10 +337,21 @@ cudaError_t ransac_score(const double* dF, int nF, const double* dx0, const doub
   double* aux = reinterpret_cast<double*>(w);             w += al256((size_t)nF * 4 * 2 * 8);
   int* valid = reinterpret_cast<int*>(w);                 w += al256((size_t)nF * 4);
   int* counts = reinterpret_cast<int*>(w);                w += al256((size_t)nF * 4 * 4);
+  int* vlist = reinterpret_cast<int*>(w);                 w += al256((size_t)nF * 4 + 16);
+  int* nvalid = vlist + nF;
   uint32_t* masks = reinterpret_cast<uint32_t*>(w);
-  ransac_setup_kernel<<<(nF + 63) / 64, 64, 0, stream>>>(dF, nF, singular_value_ratio_allowed, cams, aux, valid);
-  ransac_score_kernel<<<(unsigned)nF * 4u, RS_THREADS, 0, stream>>>(cams, aux, valid, dx0, dx1, npt, reprojection_error_allowed,
-                                                                    counts, masks, W);
+  cudaError_t e = cudaMemsetAsync(nvalid, 0, sizeof(int), stream);
+  if (e != cudaSuccess) return e;
+  int dev = 0, sms = 0;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+  ransac_setup_kernel<<<(nF + 63) / 64, 64, 0, stream>>>(dF, nF, singular_value_ratio_allowed, cams, aux, valid, counts, vlist,
+                                                         nvalid);
+  // 3 blocks of 128 threads per SM at 142 registers; the grid is that, capped by the work there can be at most
+  const long long most = (long long)nF * 4 * ((npt + RS_CHUNK - 1) / RS_CHUNK);
+  const int grid = (int)(most < (long long)sms * 3 ? most : (long long)sms * 3);
+  ransac_score_kernel<<<grid, RS_THREADS, 0, stream>>>(cams, aux, vlist, nvalid, dx0, dx1, npt, reprojection_error_allowed,
+                                                       counts, masks, W);
   ransac_pick_kernel<<<nF, 32, 0, stream>>>(valid, counts, cams, masks, W, nF, npt, required_percent_inliers,
                                             find_best_even_in_failure ? 1 : 0, dok, dcount, dcams, dmasks);
   count_launch(3);

@@ -89,3 +89,30 @@ def test_castle_cascade_recall(po):
     with np.errstate(divide="ignore", invalid="ignore"):
         want = cd[:, 1] / cd[:, 0].astype("float64") >= 1.75
     assert (my == np.nonzero(want)[0]).all() and (mx == ci[:, 0][want]).all()
+
+
+@pytest.mark.gpu
+def test_castle_quantised_dictionary_costs_no_recall():
+    """SURVEY 8d parity gate for the cascade: the drop-in draws its hyperplanes from N(0, 1) rounded to q / 32 (so that the
+    projection is an exact integer GEMM on the tensor cores); the reference's are plain fp32 N(0, 1).  On the castle
+    pair's real SIFT rows, same seed, same (m, n, g): recall@1 and @2 against the reference's exact brute-force output
+    must not drop by more than 1 % (CPU-oracle check of round 1: 0.9505 / 0.9951 vs 0.9496 / 0.9952 at m = 10)."""
+    import torch
+    from spectavi_b200 import device as dev, feature
+    g, s1, s2 = _castle()
+    _, _, _x, _y = _step2_inputs(feature, s1, s2)
+    xu = torch.from_numpy((_x + 128).astype("uint8")).cuda()
+    yu = torch.from_numpy((_y + 128).astype("uint8")).cuda()
+    want = g["idx"].astype(np.uint64)
+    m = int(np.floor(np.log2(max(_x.shape[0], _y.shape[0]) / 6.)))
+    for seed in (1, 2, 3):
+        rec = {}
+        for quantize in (True, False):
+            d = torch.from_numpy(dev.cascade_dictionary(_x.shape[1], m, 2, seed=seed, quantize=quantize))
+            keys = dev.new_keys(_y.shape[0], "cuda")
+            ws = dev.cascade_fold(xu, yu, keys, d, 2, 0)
+            gi, _ = dev.keys_finalize(keys, 2, torch.float32)
+            gi = gi.cpu().numpy().view(np.uint64)
+            del ws
+            rec[quantize] = ((gi[:, 0] == want[:, 0]).mean(), (gi == want).mean())
+        assert rec[True][0] >= rec[False][0] - 0.01 and rec[True][1] >= rec[False][1] - 0.01, (seed, rec)
