@@ -229,7 +229,7 @@ constexpr int RS_CHUNK = 4 * RS_THREADS;   // matches per work item
 // Persistent blocks over work items (gated-in hypothesis, camera, chunk of 512 matches): every thread takes 4 matches
 // of the chunk.  counts[h][c] (zeroed by the setup kernel) collects the chunk counts; masks[(h * 4 + c) * W + word]
 // (bit = match & 31) are written whole words at a time, one warp per word.
-__global__ void __launch_bounds__(RS_THREADS) ransac_score_kernel(const double* __restrict__ cams, const double* __restrict__ aux,
+__global__ void __launch_bounds__(RS_THREADS, 4) ransac_score_kernel(const double* __restrict__ cams, const double* __restrict__ aux,
                                                                   const int* __restrict__ vlist, const int* __restrict__ nvalid,
                                                                   const double* __restrict__ x0, const double* __restrict__ x1,
                                                                   int npt, double err_allowed, int* __restrict__ counts,
@@ -347,9 +347,9 @@ cudaError_t ransac_score(const double* dF, int nF, const double* dx0, const doub
   if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
   ransac_setup_kernel<<<(nF + 63) / 64, 64, 0, stream>>>(dF, nF, singular_value_ratio_allowed, cams, aux, valid, counts, vlist,
                                                          nvalid);
-  // 3 blocks of 128 threads per SM at 142 registers; the grid is that, capped by the work there can be at most
+  // 4 blocks of 128 threads per SM (128 registers); the grid is that, capped by the work there can be at most
   const long long most = (long long)nF * 4 * ((npt + RS_CHUNK - 1) / RS_CHUNK);
-  const int grid = (int)(most < (long long)sms * 3 ? most : (long long)sms * 3);
+  const int grid = (int)(most < (long long)sms * 4 ? most : (long long)sms * 4);
   ransac_score_kernel<<<grid, RS_THREADS, 0, stream>>>(cams, aux, vlist, nvalid, dx0, dx1, npt, reprojection_error_allowed,
                                                        counts, masks, W);
   ransac_pick_kernel<<<nF, 32, 0, stream>>>(valid, counts, cams, masks, W, nF, npt, required_percent_inliers,
