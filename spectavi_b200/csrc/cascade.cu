@@ -26,6 +26,7 @@
 #include <cuda_bf16.h>
 #include <cstdint>
 #include <cstdlib>
+#include <cstring>
 
 namespace spv {
 namespace {
@@ -311,6 +312,7 @@ struct HqParams {
   const int8_t* img;             // [groups][dim/16][N][16] int8 hyperplane coefficients * 32
   const int32_t* colsum;         // [groups][N]  sum_k q(k, col)
   int rows, dim, n, m, MP, tpg, N, groups, g, nst, tmem_cols;
+  int swz;                       // 1: row tiles come as 128-byte-wide SWIZZLE_128B panels (dim % 128 == 0)
   int32_t* codes;                // [n][rows]
   unsigned long long* flips;     // [n][rows]
 };
@@ -349,6 +351,17 @@ __device__ __forceinline__ void tma_load_rows(uint32_t dst, const CUtensorMap* m
       "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
       ::"r"(dst), "l"(map), "r"(0), "r"(row0), "r"(0), "r"(bar)
       : "memory");
+}
+__device__ __forceinline__ void tma_load_panel_2d(uint32_t dst, const CUtensorMap* map, int col0, int row0, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(map), "r"(col0), "r"(row0), "r"(bar)
+      : "memory");
+}
+// UMMA descriptor of a K-major SWIZZLE_128B operand: rows are 128 B apart, 8-row groups (the swizzle atom) 1024 B
+// (SBO); LBO is unused when one instruction's K extent (32 B here) lies inside the 128-byte atom; layout type 2
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 // kind::i8: D int32 (c_format = 2 at bits [4,6)), A uint8 (a_format = 0 at [7,10)), B int8 (b_format = 1 at
 // [10,13)), both K-major, N >> 3 at [17,23), M >> 4 at [24,29); K = 32 per instruction
@@ -402,6 +415,8 @@ __device__ __forceinline__ void hq_epilogue_table(uint32_t taddr, const int32_t*
     unsigned long long flips = 0;
     if (nb <= 2) {
       // the default probe depth (g = 2): both minima in ONE pass, 3 min / max per key
+      // (VIMNMX issues at 5.6 T/s on this GPU against 18 T/s for other ALU ops -- pipe_peak.cu -- and this loop is what
+      // keeps the query side ALU-bound; spelling it as setp + selp does not help: ptxas folds those back into VIMNMX)
       uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
 #pragma unroll
       for (int b = 0; b < MP; ++b) {
@@ -428,9 +443,10 @@ __device__ __forceinline__ void hq_epilogue_table(uint32_t taddr, const int32_t*
 }
 
 __global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __grid_constant__ CUtensorMap tmA, const HqParams P) {
-  extern __shared__ __align__(128) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // the swizzle atom wants 1024-byte alignment
   const int dim = P.dim, N = P.N, nst = P.nst;
-  const uint32_t stage_bytes = (uint32_t)HP_ROWS * dim;      // [dim/16][128 rows][16 B]
+  const uint32_t stage_bytes = (uint32_t)HP_ROWS * dim;      // [dim/16][128 rows][16 B], or dim/128 swizzled panels of [128 rows][128 B]
   unsigned char* sA = smem;
   unsigned char* sB = sA + (size_t)nst * stage_bytes;         // [dim/16][N][16 B]
   int32_t* sCol = reinterpret_cast<int32_t*>(sB + (size_t)dim * N);
@@ -473,7 +489,13 @@ __global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __gri
           const uint32_t it = it0 + j, s = it % nst, ph = (it / nst) & 1u;
           mbar_wait(bar_empty + 8 * s, ph ^ 1u);
           mbar_expect_tx(bar_full + 8 * s, stage_bytes);
-          tma_load_rows(smem_u32(sA) + s * stage_bytes, &tmA, (blockIdx.x + j * gridDim.x) * HP_ROWS, bar_full + 8 * s);
+          const int row0 = (blockIdx.x + j * gridDim.x) * HP_ROWS;
+          if (P.swz) {
+            for (int pnl = 0; pnl < dim / 128; ++pnl)
+              tma_load_panel_2d(smem_u32(sA) + s * stage_bytes + pnl * (HP_ROWS * 128), &tmA, pnl * 128, row0, bar_full + 8 * s);
+          } else {
+            tma_load_rows(smem_u32(sA) + s * stage_bytes, &tmA, row0, bar_full + 8 * s);
+          }
         }
     } else if (warp == 1) {
       if (lane == 0)
@@ -484,7 +506,8 @@ __global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __gri
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a0 = smem_u32(sA) + s * stage_bytes, b0 = smem_u32(sB);
           for (int k = 0; k < dim / 32; ++k) {         // one UMMA per K = 32 bytes = two 16-byte k-chunks
-            const uint64_t ad = umma_desc(a0 + (2 * k) * (HP_ROWS * 16), HP_ROWS * 16, 128);
+            const uint64_t ad = P.swz ? umma_desc_sw128(a0 + (k >> 2) * (HP_ROWS * 128) + (k & 3) * 32)
+                                      : umma_desc(a0 + (2 * k) * (HP_ROWS * 16), HP_ROWS * 16, 128);
             const uint64_t bd = umma_desc(b0 + (2 * k) * (N * 16), N * 16, 128);
             umma_i8(tmem + a * N, ad, bd, idesc, k != 0);
           }
@@ -1003,7 +1026,10 @@ cudaError_t run_project_i8(const Plan& pl, const uint8_t* rows_u8, int rows, int
   while (cols < 2 * pl.N) cols <<= 1;
   hq.tmem_cols = cols;
   CUtensorMap tmA;
-  if (!make_rows_map(&tmA, rows_u8, rows, dim, HP_ROWS)) return cudaErrorInvalidValue;
+  const char* k2 = getenv("SPECTAVI_K2");
+  hq.swz = (dim % 128 == 0 && !(k2 && strcmp(k2, "legacy") == 0)) ? 1 : 0;
+  if (hq.swz ? !make_rows_map_sw128(&tmA, rows_u8, rows, dim, HP_ROWS) : !make_rows_map(&tmA, rows_u8, rows, dim, HP_ROWS))
+    return cudaErrorInvalidValue;
   cudaError_t e = cudaFuncSetAttribute(hash_project_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int per_sm = (smem <= 110 * 1024 && cols <= 256) ? 2 : 1;

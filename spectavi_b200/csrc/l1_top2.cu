@@ -548,6 +548,21 @@ bool make_rows_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// rows x dim uint8, row-major, as a plain 2-D map with 128-byte-wide boxes and the 128-byte swizzle: every request is
+// a whole 128-byte line (the permuted 16-byte-wide map above makes TMA fetch every line as eight 16-byte pieces: K2's
+// L2 traffic was 3.4x its DRAM traffic), and the tile lands in the canonical UMMA K-major SWIZZLE_128B layout
+bool make_rows_map_sw128(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)dim};
+  cuuint32_t box[2] = {128u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(base), gdim, gstride, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // column-major float32 matrix [dim][pitch] (pitch floats per column, rows valid), seen as 2-D (rows, dim); a box of
 // (box_rows, box_cols) lands in shared memory as [col][row]; rows / columns outside the matrix read as zeros
 bool make_f32_panel_map(CUtensorMap* map, const float* base, int rows, int dim, size_t pitch, int box_rows, int box_cols) {

@@ -49,6 +49,7 @@ cudaError_t keys_finalize_f32(const unsigned long long* keys, int yrows, int kco
 // a box of (16, box_rows, dim/16) lands in shared memory as [dim/16][box_rows][16 B], i.e. already in the
 // k-chunk-major order K1 reads and in the UMMA K-major no-swizzle core-matrix order K2 feeds to tcgen05
 bool make_rows_map(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows);
+bool make_rows_map_sw128(CUtensorMap* map, const uint8_t* base, int rows, int dim, int box_rows);
 bool make_f32_panel_map(CUtensorMap* map, const float* base, int rows, int dim, size_t pitch, int box_rows, int box_cols);
 // ---- lp_topk.cu : K1f, brute-force sum |x-y|^p top-k over float32 / int32 rows
 // (BruteForceNn.h:37-120).  partial: scratch of lp_partial_bytes(); didx/ddist:
