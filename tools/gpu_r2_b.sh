@@ -5,6 +5,7 @@ M=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_bytes
 # 1. launch list of the headline command
 B="python bench.py --steps 2 --warmup 3 --no-cpu --no-extras"
 timeout 600 $B > $O/plain_bench.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/r02_launches_c3.csv $B > $O/ncu_b.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:l1_top2_kernel -s 3 -c 1 -f -o $O/k1_full $B > $O/ncu_k1_full.log 2>&1
 # 2. K1f: TMA-fed kernel, per-launch metrics + one full capture
 L="python tools/bench_lp.py 20000 1"
 timeout 600 $L > $O/lp_20k.json 2> $O/lp.err && {
@@ -19,12 +20,12 @@ timeout 600 $C > $O/plain_c.log 2>&1 && {
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"probe_rerank" -c 1 -f -o $O/k4_full $C > $O/ncu_k4_full.log 2>&1
 }
 # 4. K8
-R="python tools/bench_ransac.py 2000 2000 32"
+R="python tools/bench_ransac.py 2000 4000 32"
 timeout 600 $R > $O/ransac.json 2> $O/ransac.err && {
   timeout 900 ncu --metrics $M --clock-control none -k regex:"ransac" -c 9 --csv --log-file $O/r02_ransac_launches.csv $R > $O/ncu_r.log 2>&1
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"ransac_score" -s 1 -c 1 -f -o $O/k8_full $R > $O/ncu_k8_full.log 2>&1
 }
-for f in k1f_tma_full k2_full k4_full k8_full; do
+for f in k1_full k1f_tma_full k2_full k4_full k8_full; do
   [ -f $O/$f.ncu-rep ] && ncu -i $O/$f.ncu-rep --page details --print-units base 2>/dev/null | grep -E "^  [a-z_0-9]+.*\(|Duration|Throughput|Pipe|Issue|Registers|Stall|dram__bytes|Hit Rate|Achieved Occupancy|Theoretical Occupancy|Executed Ipc|L2 Cache|DRAM|Shared Memory|Bank" > $O/r02_${f}_summary.txt
 done
 cat $O/lp_20k.json | cut -c1-1500; tail -2 $O/lp.err; cat $O/ransac.json | cut -c1-1200; tail -1 $O/plain_c.log | cut -c1-1500
