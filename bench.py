@@ -77,6 +77,15 @@ def workload_text(wname, xr, yr, dim, world):
         wname, xr, yr, dim, "" if world == 1 else ", train sharded %d-way + NCCL all-gather + top-2 merge" % world)
 
 
+def config_of(wname, xr, yr, dim, world):
+    """The SAME dictionary in both arms (the driver compares them): what differs between the arms -- how a step is
+    sampled and timed -- is in `arm_notes` and `cpu_baseline.sample`."""
+    return {"workload": workload_text(wname, xr, yr, dim, world),
+            "l2": "GPU arm: L2 flushed between timed steps by a %d MiB fill outside the event pair; reference arm: host cores, n/a" % (L2_FLUSH_BYTES >> 20),
+            "timing": "GPU arm: CUDA events per step on the launching stream, summed, max over ranks; reference arm: perf_counter around the K steps",
+            "sample": "GPU arm: the full workload every step; reference arm: a bounded slice of query rows x all train rows per step (rows are independent), see cpu_baseline.sample"}
+
+
 def host_rows(rows, dim, seed, lo=0):
     """Synthetic uniform u8 descriptors (test/test_feature.py:112-115's distribution),
     generated in 64k-row blocks keyed by (seed, block) so that any shard of any
@@ -238,8 +247,7 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "strong" if ngpu > 1 else "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic uniform u8 (Philox, seeded per 64k-row block)",
-            "config": {"workload": workload_text(wname, xr, yr, dim, ngpu),
-                       "l2": "n/a (host cores)", "timing": "perf_counter around the K steps", "sample": sample},
+            "config": config_of(wname, xr, yr, dim, ngpu), "arm_notes": {"sample": sample, "timing": "perf_counter around the K steps"},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "extras": extras}
@@ -636,10 +644,8 @@ def run_b200(args):
             "warmup": max(args.warmup, 3) if args.warmup else 0, "ms_per_step": step_ms / args.steps,
             "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic uniform u8 (Philox, seeded per 64k-row block)",
-            "config": {"workload": workload_text(wname, xr, yr, dim, world),
-                       "l2": "L2 flushed between timed steps by a %d MiB fill outside the event pair" % (L2_FLUSH_BYTES >> 20),
-                       "timing": "CUDA events per step on the launching stream, summed, max over ranks",
-                       "sample": "full workload every step"},
+            "config": config_of(wname, xr, yr, dim, world),
+            "arm_notes": {"sample": "full workload every step", "timing": "CUDA events per step on the launching stream, summed, max over ranks"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(l1 - l0), "roofline": roof, "cpu_baseline": cpu}
     line.update(parity)
     if extras:
