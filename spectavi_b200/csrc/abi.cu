@@ -249,7 +249,7 @@ void spv_normalize_to_ubyte(const float* x, int rows, int dim, NdArray* out) {
 }
 
 static void lp_entry(const char* fn, const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k,
-                     float p, NdArray* outidx, NdArray* outdist) {
+                     float p, float mu, NdArray* outidx, NdArray* outdist) {
   if (xrows < 0 || yrows < 0 || dim <= 0) die(fn, "bad shape %d x %d x %d", xrows, yrows, dim);
   if (k < 1) die(fn, "k = %d must be >= 1", k);
   out_alloc(outidx, (uint64_t)yrows, (uint64_t)k);    // Spectavi.cpp:262-265 / :275-278
@@ -257,18 +257,17 @@ static void lp_entry(const char* fn, const void* x, const void* y, bool is_int, 
   if (yrows == 0) return;
   HostCall hc(fn);
   // BruteForceNn's ctor takes `double p` (BruteForceNn.h:26-28): the float widens exactly
-  hc.lpk(x, y, is_int, xrows, yrows, dim, k, (double)p, reinterpret_cast<uint64_t*>(outidx->m_data), outdist->m_data);
+  hc.lpk(x, y, is_int, xrows, yrows, dim, k, (double)p, reinterpret_cast<uint64_t*>(outidx->m_data), outdist->m_data, mu);
 }
 
 void nn_bruteforce(const float* x, const float* y, int xrows, int yrows, int dim, int k, float p, float mu,
                    NdArray* outidx, NdArray* outdist) {
-  (void)mu;   // the reference's approximate prune knob (BruteForceNn.h:82-86); results here are exact
-  lp_entry("nn_bruteforce", x, y, false, xrows, yrows, dim, k, p, outidx, outdist);
+  // mu != 0 is the reference's approximate prune (BruteForceNn.h:80-86): emulated in its visiting order (lp_topk_mu)
+  lp_entry("nn_bruteforce", x, y, false, xrows, yrows, dim, k, p, mu, outidx, outdist);
 }
 void nn_bruteforcei(const int* x, const int* y, int xrows, int yrows, int dim, int k, float p, float mu,
                     NdArray* outidx, NdArray* outdist) {
-  (void)mu;
-  lp_entry("nn_bruteforcei", x, y, true, xrows, yrows, dim, k, p, outidx, outdist);
+  lp_entry("nn_bruteforcei", x, y, true, xrows, yrows, dim, k, p, mu, outidx, outdist);
 }
 // ---- Part 1c: the filter overload of the generic matcher and the caller that drives it
 void spv_nn_bruteforce_filtered(const float* x, const float* y, int xrows, int yrows, int dim, int k, float p, float mu,

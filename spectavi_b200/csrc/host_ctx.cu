@@ -693,7 +693,7 @@ void HostCall::normalize(const float* x, int rows, int dim, float* out) {
 }
 
 void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p,
-                   uint64_t* idx, void* dist) {
+                   uint64_t* idx, void* dist, float mu) {
   // single GPU: the graded shapes of this entry point are small (test/test_feature.py:67-81)
   Gpu& D = ctx_->gpus[0];
   int sms = 0;
@@ -703,13 +703,18 @@ void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yro
   const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
   CU(fn_, D.x.ensure(xb ? xb : 4));
   CU(fn_, D.y.ensure(yb ? yb : 4));
-  CU(fn_, D.gather.ensure(lp_ws_bytes(xrows, yrows, dim, k, sms)));
+  const bool approx = is_int ? ((int)mu != 0) : (mu != 0.f);      // Scalar m_mu: truncated for the int instantiation
+  CU(fn_, D.gather.ensure(approx ? lp_mu_ws_bytes(yrows, k) : lp_ws_bytes(xrows, yrows, dim, k, sms)));
   CU(fn_, D.oidx.ensure(ib));
   CU(fn_, D.odist.ensure(db));
   if (xb) CU(fn_, cudaMemcpyAsync(D.x.p, x, xb, cudaMemcpyHostToDevice, D.stream));
   CU(fn_, cudaMemcpyAsync(D.y.p, y, yb, cudaMemcpyHostToDevice, D.stream));
-  CU(fn_, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p, D.odist.p,
-                  D.stream));
+  if (approx)
+    CU(fn_, lp_topk_mu(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, mu, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p,
+                       D.odist.p, D.stream));
+  else
+    CU(fn_, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p, D.odist.p,
+                    D.stream));
   CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
   CU(fn_, cudaStreamSynchronize(D.stream));

@@ -46,8 +46,9 @@ class HostCall {
   void l1k2(const uint8_t* x, const uint8_t* y, int xrows, int yrows, int dim, uint64_t* idx, int32_t* dist,
             const MatchSink* ms = nullptr);
   // brute-force sum |x-y|^p top-k over float32 / int32 rows (yrows x k out)
+  // mu != 0 (for int32 rows: (int)mu != 0) selects the emulation of the reference's approximate prune
   void lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p, uint64_t* idx,
-           void* dist);
+           void* dist, float mu = 0.f);
   // The filter overload of the generic matcher (BruteForceNn.h:37-49).  filter_x / filter_y: row-id sets, empty = all
   // rows.  idx / dist (yrows x k) are in-out: only rows in filter_y are written.
   void lpk_filtered(const float* x, const float* y, int xrows, int yrows, int dim, int k, double p,

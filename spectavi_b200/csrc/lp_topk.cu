@@ -533,6 +533,91 @@ cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int 
   return cudaSuccess;
 }
 
+// ---- mu != 0: the reference's approximate search, emulated operation for operation ----------------------------
+// BruteForceNn.h:80-86 prunes a train row as soon as `distp + mu * (dim - icol - 1) > worst`: an early exit that,
+// for mu != 0, also drops rows that WOULD have entered the top k -- and which rows depends on the order they were
+// visited in and on the running worst distance, so the only way to return the reference's result is to walk the
+// train rows in its order.  One thread per query row, sequential over train rows and columns, the k best in a
+// sorted array (only the heap's top and size are ever observed, oracle/spv_oracle.c); float accumulation with
+// unfused IEEE operations.  A search of n x n rows costs n * dim sequential steps per thread -- fine for the shapes
+// an approximation knob is used on, and the exact matcher (mu == 0) never comes here.
+template <typename T>
+__global__ void lp_topk_mu_kernel(const T* __restrict__ x, const T* __restrict__ y, int xrows, int yrows, int dim, int k, double p,
+                                  float mu_f, unsigned long long* __restrict__ sets, uint64_t* __restrict__ idx,
+                                  T* __restrict__ dist) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= yrows) return;
+  unsigned long long* S = sets + (size_t)r * (k + 1);     // ascending (dist bits << 32 | idx); dist >= 0 so bits order = value order
+  const T* yr = y + (size_t)r * dim;
+  const int pm = (p == 1.0) ? P_ONE : (p == 2.0) ? P_TWO : (p == 0.5) ? P_HALF : P_POW;
+  const int mu_i = (int)mu_f;                             // Scalar m_mu with Scalar = int (BruteForceNn.h:28)
+  int n = 0;
+  bool have_worst = false;
+  T worst = (T)0;
+  for (int c = 0; c < xrows; ++c) {
+    const T* xr = x + (size_t)c * dim;
+    T acc = (T)0;
+    bool pruned = false;
+    for (int j = 0; j < dim; ++j) {
+      if constexpr (std::is_same<T, float>::value) {
+        const float d = __fsub_rn(xr[j], yr[j]);
+        float t;
+        if (pm == P_ONE) t = fabsf(d);
+        else if (pm == P_TWO) t = __fmul_rn(d, d);
+        else if (pm == P_HALF) t = sqrtf(fabsf(d));
+        else t = (float)pow((double)fabsf(d), p);
+        acc = __fadd_rn(acc, t);
+        if (have_worst && __fadd_rn(acc, __fmul_rn(mu_f, (float)(dim - (j + 1)))) > worst) { pruned = true; break; }
+      } else {
+        const float d = (float)(xr[j] - yr[j]);
+        if (pm == P_POW) acc += __double2int_rz(pow((double)fabsf(d), p));
+        else acc += __float2int_rz(pm == P_ONE ? fabsf(d) : pm == P_TWO ? __fmul_rn(d, d) : sqrtf(fabsf(d)));
+        if (have_worst && acc + mu_i * (dim - (j + 1)) > worst) { pruned = true; break; }
+      }
+    }
+    if (pruned) continue;
+    // :93-108 (a candidate that is not strictly better than a full heap's worst is rejected: the reference's
+    // push-without-pop there is undefined behaviour)
+    if (have_worst && !(acc < worst)) continue;
+    if (have_worst && n >= k) --n;                        // pop the largest
+    const unsigned long long key = ((unsigned long long)dist_bits(acc) << 32) | (uint32_t)c;
+    int pos = n;
+    while (pos > 0 && S[pos - 1] > key) { S[pos] = S[pos - 1]; --pos; }
+    S[pos] = key;
+    ++n;
+    if (have_worst || n == k) {
+      have_worst = true;
+      const uint32_t b = (uint32_t)(S[n - 1] >> 32);
+      if constexpr (std::is_same<T, float>::value) worst = __uint_as_float(b);
+      else worst = (int)b;
+    }
+  }
+  for (int q = 0; q < n; ++q) {                           // :111-118, right-aligned
+    const int col = k - n + q;
+    idx[(size_t)r * k + col] = S[q] & 0xFFFFFFFFull;
+    const uint32_t b = (uint32_t)(S[q] >> 32);
+    if constexpr (std::is_same<T, float>::value) dist[(size_t)r * k + col] = __uint_as_float(b);
+    else dist[(size_t)r * k + col] = (int)b;
+  }
+}
+
+size_t lp_mu_ws_bytes(int yrows, int k) { return (size_t)(yrows > 0 ? yrows : 0) * (size_t)(k + 1) * sizeof(unsigned long long) + 8; }
+
+cudaError_t lp_topk_mu(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p, float mu,
+                       void* ws, size_t ws_bytes, uint64_t* didx, void* ddist, cudaStream_t stream) {
+  if (yrows <= 0) return cudaSuccess;
+  if (k < 1 || dim < 1 || ws_bytes < lp_mu_ws_bytes(yrows, k)) return cudaErrorInvalidValue;
+  cudaError_t e = cudaMemsetAsync(didx, 0, (size_t)yrows * k * sizeof(uint64_t), stream);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(ddist, 0, (size_t)yrows * k * 4, stream);
+  if (e != cudaSuccess || xrows <= 0) return e;
+  unsigned long long* sets = static_cast<unsigned long long*>(ws);
+  if (is_int) lp_topk_mu_kernel<int><<<(yrows + 63) / 64, 64, 0, stream>>>((const int*)dx, (const int*)dy, xrows, yrows, dim, k, p, mu, sets, didx, (int*)ddist);
+  else lp_topk_mu_kernel<float><<<(yrows + 63) / 64, 64, 0, stream>>>((const float*)dx, (const float*)dy, xrows, yrows, dim, k, p, mu, sets, didx, (float*)ddist);
+  count_launch();
+  return cudaGetLastError();
+}
+
 // ---- the filter overload, batched over groups (see the header)
 int lp_filtered_tile_rows() { return TB; }
 

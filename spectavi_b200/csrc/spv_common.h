@@ -62,6 +62,11 @@ size_t lp_ws_bytes(int xrows, int yrows, int dim, int k, int sms);
 // environment says SPECTAVI_K1F=v1), otherwise -- and for int32 rows, k > LP_MAX_K -- the register-staged one
 cudaError_t lp_topk(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p,
                     void* ws, size_t ws_bytes, uint64_t* didx, void* ddist, cudaStream_t stream);
+// mu != 0 (BruteForceNn.h:80-86, the reference's approximate prune): a sequential-per-query emulation that returns
+// the reference's result, not the exact top-k
+size_t lp_mu_ws_bytes(int yrows, int k);
+cudaError_t lp_topk_mu(const void* dx, const void* dy, bool is_int, int xrows, int yrows, int dim, int k, double p, float mu,
+                       void* ws, size_t ws_bytes, uint64_t* didx, void* ddist, cudaStream_t stream);
 // lp_topk_tma.cu
 size_t lp_tma_ws_bytes(int xrows, int yrows, int dim, int k, int sms);
 cudaError_t lp_topk_tma(const float* dx, const float* dy, int xrows, int yrows, int dim, int k, double p, void* ws,

@@ -20,9 +20,8 @@ def test_bruteforce_golden(feature):
     g = golden("bruteforce_300x250x132.npz")
     x, y = g["x"], g["y"]
     for tag, p, k in (("p2", 2., 2), ("p1", 1., 2), ("p05", .5, 2), ("p2k5", 2., 5), ("p2mu", 2., 2)):
-        gi, gd = feature.nn_bruteforce(x, y, p=p, mu=0., k=k)
-        if tag == "p2mu":
-            continue   # mu != 0 is the reference's approximation knob; exact results are checked via p2
+        # p2mu: mu = .05, the reference's approximate prune (BruteForceNn.h:80-86), emulated in its visiting order
+        gi, gd = feature.nn_bruteforce(x, y, p=p, mu=.05 if tag == "p2mu" else 0., k=k)
         assert (gi == g["idx_" + tag]).all(), tag
         assert (gd.view(np.uint32) == g["dist_" + tag].view(np.uint32)).all(), tag
     gi, gd = feature.nn_bruteforce(x, y, p=1.5, mu=0., k=2)
@@ -175,3 +174,20 @@ def test_bruteforce_tma_kernel_equals_register_staged_kernel(po, feature, shape,
     if p != 1.5:
         oi, od = po.bruteforce(x, y, k, p, 0.)
         assert (gi.reshape(oi.shape) == oi).all() and (gd.reshape(od.shape).view(np.uint32) == od.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("p,mu,k,use_int", [(2., .05, 2, False), (1., .3, 3, False), (.5, .02, 1, False), (2., 1.5, 2, True),
+                                             (1., 2.0, 4, True), (2., -.1, 2, False)])
+def test_bruteforce_mu_equals_reference_semantics(po, feature, p, mu, k, use_int):
+    """mu != 0 makes the reference's search approximate: a train row is dropped as soon as
+    distp + mu * (columns left) > worst, which depends on the visiting order.  The library walks the rows in the
+    reference's order (one thread per query row), so idx and dist equal the oracle's restatement (itself checked
+    against the reference build and its golden vector) bit for bit -- and differ from the exact top-k."""
+    rng = np.random.RandomState(int(p * 10) + k)
+    x = rng.randn(700, 36).astype("float32")
+    y = rng.randn(90, 36).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=p, mu=mu, k=k, use_int=use_int)
+    xs, ys = (np.round(100 * x).astype("int32"), np.round(100 * y).astype("int32")) if use_int else (x, y)
+    oi, od = po.bruteforce(xs, ys, k, p, mu, use_int=use_int)
+    assert (gi.reshape(oi.shape) == oi).all()
+    assert (gd.reshape(od.shape).view(np.uint32) == od.view(np.uint32)).all()
