@@ -61,7 +61,8 @@ void nn_bruteforcel1k2(const uint8_t *x, const uint8_t *y, int xrows, int yrows,
 /* replaces src/Spectavi.cpp:258-269 (BruteForceNn<float>, src/BruteForceNn.h:37-120).
  * k nearest under sum |d|^p (p == 1, 2, .5 special-cased, otherwise powf);
  * outidx yrows x k size_t, outdist yrows x k float32, ascending.  mu != 0 (the
- * reference's approximate prune) is accepted and computed exactly. */
+ * reference's approximate, visiting-order-dependent prune, :80-86) is emulated in the
+ * reference's order and returns the reference's result; mu == 0 takes the fast kernels. */
 void nn_bruteforce(const float *x, const float *y, int xrows, int yrows, int dim, int k, float p, float mu,
                    NdArray *outidx, NdArray *outdist);
 
