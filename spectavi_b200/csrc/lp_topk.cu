@@ -18,7 +18,7 @@
 // it pushes without popping and later stores to column -1 (:102-108,:111-118;
 // undefined behaviour); such a candidate is rejected here.
 // The early-exit prune (:82-86) is exact for mu == 0 and never changes the
-// result; mu != 0 (an approximation knob) is accepted and computed exactly.
+// result; mu != 0 (an order-dependent approximation) is emulated by lp_topk_mu_kernel at the end of this file.
 //
 // Bound: FP32 CUDA-core pipe, 2 (p=1) or 3 (p=2) dependent-free ops per element.
 //
