@@ -53,6 +53,7 @@ struct PinBuf {
 // memcpy) -> device (DMA); with two buffers the memcpy of sub-chunk i + 1 runs under the DMA of sub-chunk i,
 // and -- because the DMA sits on its own stream -- under whatever the compute stream is doing.
 constexpr size_t LANE_BYTES = (size_t)4 << 20;
+constexpr int NLANE = 8;                       // lanes that exist; upload_lanes() says how many a float upload uses
 struct Lane {
   cudaStream_t copy = nullptr;
   void* pin[2] = {nullptr, nullptr};
@@ -65,7 +66,7 @@ struct Lane {
 struct Gpu {
   int dev = -1;
   cudaStream_t stream = nullptr;
-  Lane lane[4];
+  Lane lane[NLANE];
   bool lanes_ready = false;
   cudaEvent_t ev[16] = {};      // scratch events (per-chunk completion of the final pass)
   Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws, rws, sel;
@@ -215,11 +216,11 @@ void lanes_init(const char* fn, Gpu& D) {
 
 // pageable host -> device through the lane's pinned buffers; returns once the last sub-chunk is QUEUED.
 // The device's current-device must be D's.  `ready` is recorded behind the piece.
-void lane_upload(const char* fn, Lane& L, void* dst, const void* src, size_t bytes) {
+void lane_upload(const char* fn, Lane& L, void* dst, const void* src, size_t bytes, size_t sub = LANE_BYTES) {
   const char* s = static_cast<const char*>(src);
   char* d = static_cast<char*>(dst);
-  for (size_t off = 0; off < bytes; off += LANE_BYTES) {
-    const size_t n = bytes - off < LANE_BYTES ? bytes - off : LANE_BYTES;
+  for (size_t off = 0; off < bytes; off += sub) {
+    const size_t n = bytes - off < sub ? bytes - off : sub;
     const int b = L.turn;
     L.turn ^= 1;
     if (L.used[b]) CU(fn, cudaEventSynchronize(L.done[b]));
@@ -360,15 +361,31 @@ void l1k2_stream_shard(const char* fn, Gpu& D, const uint8_t* x, const uint8_t* 
   }
 }
 
+// Host threads (= lanes) of one pageable upload.  Measured on the box (a 16-core VM; tools/bench_e2e_lanes.py on C5's
+// 1 GB of float rows): 1 lane 11.5 GB/s, 2 lanes 21.6, 4 lanes 36.7, 6 lanes 38.8, 8 lanes 37.7.  The scheme in
+// isolation (tools/ubench_stage_mt.cu): a memcpy thread alone moves 12-19 GB/s, the DMA alone 50-55 GB/s, together they
+// share the host's memory system -- 256 MB: 40 GB/s with 4 threads, 43 with 6; 21 MB: 0.87 ms with 4 threads and
+// 1 MB sub-chunks, no better with more (the DMAs only drain once the copy threads are done).  SPECTAVI_UPLOAD_LANES
+// overrides.
+int upload_lanes() {
+  static const int n = [] {
+    const char* e = getenv("SPECTAVI_UPLOAD_LANES");
+    int v = e ? atoi(e) : 4;
+    return v < 1 ? 1 : (v > NLANE ? NLANE : v);
+  }();
+  return n;
+}
+
 // float32 rows -> device uint8 (value + 128): upload through `nl` lanes in parallel (each lane streams a
 // contiguous slice of the rows with its own host thread, so the pageable -> pinned memcpy -- the slow half of
-// the path at ~10 GB/s per thread -- runs nl-wide), K0 converts each sub-chunk on the lane's stream as it lands
-// (CascadingHashNn.h:236-239), and the compute stream waits for every lane.  dtmp: nl * 2 * LANE_BYTES of scratch.
+// the path -- runs nl-wide), K0 converts each sub-chunk on the lane's stream as it lands
+// (CascadingHashNn.h:236-239), and the compute stream waits for every lane.  dtmp: NLANE * 2 * LANE_BYTES of scratch.
 void upload_f32_as_u8(const char* fn, Gpu& D, const float* src, size_t count, uint8_t* dst, float* dtmp) {
   lanes_init(fn, D);
   const size_t per_chunk = LANE_BYTES / 4;                     // floats per sub-chunk
   const size_t nchunks = (count + per_chunk - 1) / per_chunk;
-  int nl = (int)(nchunks < 4 ? (nchunks ? nchunks : 1) : 4);
+  const size_t want = (size_t)upload_lanes();
+  int nl = (int)(nchunks < want ? (nchunks ? nchunks : 1) : want);
   auto work = [&](int li) {
     cudaSetDevice(D.dev);
     Lane& L = D.lane[li];
@@ -603,7 +620,7 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
     CU(fn, D.keys.ensure((size_t)2 * yrows * sizeof(unsigned long long)));
     CU(fn, D.dict.ensure(hdict.size() * 4));
     CU(fn, D.ws.ensure(wsb));
-    CU(fn, D.xf.ensure((size_t)4 * 2 * LANE_BYTES));   // device twins of the pinned staging buffers
+    CU(fn, D.xf.ensure((size_t)NLANE * 2 * LANE_BYTES));   // device twins of the pinned staging buffers
     CU(fn, cudaMemcpyAsync(D.dict.p, hdict.data(), hdict.size() * 4, cudaMemcpyHostToDevice, D.stream));
     CU(fn, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
     if (xn > 0) {
@@ -631,6 +648,72 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
   fetch_results(fn_, c, R, idx, R.oidx.p, ib, dist, R.odist.p, db);
 }
 
+// ---- single-GPU entry points: pageable <-> device without the driver's slow paths ----------------------------
+// Upload: arrays of a few MB go through the driver's own staging (one call, nothing to coordinate); larger ones are
+// cut into one contiguous part per upload lane (thread + copy stream + two pinned buffers), and the compute stream
+// waits for every lane.  Download: the DMAs land in pinned memory and copy_out moves them on (a direct device ->
+// pageable copy runs at ~2 GB/s, see copy_out).
+struct Down { void* h; const void* d; size_t bytes; };
+struct Up { void* d; const void* h; size_t bytes; };
+
+// The arrays of `items` are treated as one run of bytes and cut into one part per lane, so that two 10 MB matrices
+// keep every lane busy; a part goes up in 1 MB sub-chunks (a single memcpy thread moves 5-8 GB/s on the box: with
+// 4 MB sub-chunks the first DMA would only start after ~0.6 ms).
+void upload(const char* fn, Gpu& D, std::initializer_list<Up> items) {
+  size_t total = 0;
+  for (const Up& it : items) total += it.bytes;
+  if (total < ((size_t)1 << 20)) {
+    for (const Up& it : items)
+      if (it.bytes) CU(fn, cudaMemcpyAsync(it.d, it.h, it.bytes, cudaMemcpyHostToDevice, D.stream));
+    return;
+  }
+  lanes_init(fn, D);
+  const size_t grain = (size_t)256 << 10, ngrains = (total + grain - 1) / grain, want = (size_t)upload_lanes();
+  const int nl = (int)(ngrains / 2 < want ? (ngrains / 2 ? ngrains / 2 : 1) : want);   // at least 512 KB per lane
+  const size_t sub = total / nl >= 2 * LANE_BYTES ? LANE_BYTES : ((size_t)1 << 20);
+  const std::vector<Up> v(items);
+  const Trace tr;
+  auto work = [&](int li) {
+    cudaSetDevice(D.dev);
+    tr("upload lane starts", li);
+    const size_t b0 = ngrains * li / nl * grain, b1 = li + 1 == nl ? total : ngrains * (li + 1) / nl * grain;
+    size_t pos = 0;                                       // start of the current array in the run
+    for (const Up& it : v) {
+      const size_t lo = b0 > pos ? b0 : pos, hi = b1 < pos + it.bytes ? b1 : pos + it.bytes;
+      if (lo < hi) lane_upload(fn, D.lane[li], static_cast<char*>(it.d) + (lo - pos), static_cast<const char*>(it.h) + (lo - pos), hi - lo, sub);
+      pos += it.bytes;
+    }
+    tr("upload lane queued its last sub-chunk", li, (long long)(b1 - b0));
+  };
+  std::vector<std::thread> th;
+  for (int li = 1; li < nl; ++li) th.emplace_back(work, li);
+  work(0);
+  for (std::thread& t : th) t.join();
+  for (int li = 0; li < nl; ++li) CU(fn, cudaStreamWaitEvent(D.stream, D.lane[li].ready, 0));
+  tr("upload joined");
+}
+void upload(const char* fn, Gpu& D, void* dst, const void* src, size_t bytes) { upload(fn, D, {{dst, src, bytes}}); }
+
+// queues the DMAs behind D.stream's work, waits for the stream, delivers
+void download(const char* fn, Gpu& D, std::initializer_list<Down> items) {
+  size_t total = 0;
+  for (const Down& it : items) total += (it.bytes + 255) & ~(size_t)255;
+  if (!total) { CU(fn, cudaStreamSynchronize(D.stream)); return; }
+  CU(fn, D.res.ensure(total));
+  char* pin = static_cast<char*>(D.res.p);
+  size_t o = 0;
+  for (const Down& it : items) {
+    if (it.bytes) CU(fn, cudaMemcpyAsync(pin + o, it.d, it.bytes, cudaMemcpyDeviceToHost, D.stream));
+    o += (it.bytes + 255) & ~(size_t)255;
+  }
+  CU(fn, cudaStreamSynchronize(D.stream));
+  o = 0;
+  for (const Down& it : items) {
+    if (it.bytes) copy_out(it.h, pin + o, it.bytes);
+    o += (it.bytes + 255) & ~(size_t)255;
+  }
+}
+
 int HostCall::ransac(const double* x0, const double* x1, int npt, double required, double err_allowed, bool find_best,
                      double sv_ratio, const double* F, int nF, bool stop_at_success, int32_t* ok, int32_t* ninlier,
                      double* cams, uint32_t* masks) {
@@ -648,22 +731,19 @@ int HostCall::ransac(const double* x0, const double* x1, int npt, double require
   CU(fn_, D.oidx.ensure((size_t)B * 8));                       // ok, ninlier
   CU(fn_, D.odist.ensure((size_t)B * 12 * 8));
   if (masks) CU(fn_, D.gather.ensure((size_t)B * W * 4));
-  CU(fn_, cudaMemcpyAsync(D.x.p, x0, pb, cudaMemcpyHostToDevice, D.stream));
-  CU(fn_, cudaMemcpyAsync(D.y.p, x1, pb, cudaMemcpyHostToDevice, D.stream));
+  upload(fn_, D, {{D.x.p, x0, pb}, {D.y.p, x1, pb}});
   int done = 0;
   while (done < nF) {
     const int nb = nF - done < B ? nF - done : B;
     int32_t* dok = (int32_t*)D.oidx.p;
     int32_t* dcnt = dok + B;
-    CU(fn_, cudaMemcpyAsync(D.xf.p, F + (size_t)done * 9, (size_t)nb * 9 * 8, cudaMemcpyHostToDevice, D.stream));
+    upload(fn_, D, D.xf.p, F + (size_t)done * 9, (size_t)nb * 9 * 8);
     CU(fn_, ransac_score((const double*)D.xf.p, nb, (const double*)D.x.p, (const double*)D.y.p, npt, required, err_allowed,
                          find_best, sv_ratio, dok, dcnt, (double*)D.odist.p, masks ? (uint32_t*)D.gather.p : nullptr, D.ws.p,
                          D.ws.cap, D.stream));
-    CU(fn_, cudaMemcpyAsync(ok + done, dok, (size_t)nb * 4, cudaMemcpyDeviceToHost, D.stream));
-    CU(fn_, cudaMemcpyAsync(ninlier + done, dcnt, (size_t)nb * 4, cudaMemcpyDeviceToHost, D.stream));
-    CU(fn_, cudaMemcpyAsync(cams + (size_t)done * 12, D.odist.p, (size_t)nb * 12 * 8, cudaMemcpyDeviceToHost, D.stream));
-    if (masks) CU(fn_, cudaMemcpyAsync(masks + (size_t)done * W, D.gather.p, (size_t)nb * W * 4, cudaMemcpyDeviceToHost, D.stream));
-    CU(fn_, cudaStreamSynchronize(D.stream));
+    download(fn_, D, {{ok + done, dok, (size_t)nb * 4}, {ninlier + done, dcnt, (size_t)nb * 4},
+                      {cams + (size_t)done * 12, D.odist.p, (size_t)nb * 12 * 8},
+                      {masks ? masks + (size_t)done * W : nullptr, D.gather.p, masks ? (size_t)nb * W * 4 : 0}});
     done += nb;
     if (stop_at_success) {
       bool hit = false;
@@ -686,10 +766,9 @@ void HostCall::normalize(const float* x, int rows, int dim, float* out) {
   CU(fn_, D.xf.ensure(ib));
   CU(fn_, D.yf.ensure(ob));
   CU(fn_, D.rws.ensure(normalize_ws_bytes(dim)));
-  CU(fn_, cudaMemcpyAsync(D.xf.p, x, ib, cudaMemcpyHostToDevice, D.stream));
+  upload(fn_, D, D.xf.p, x, ib);
   CU(fn_, normalize_rows((const float*)D.xf.p, rows, dim, (float*)D.yf.p, nullptr, D.rws.p, D.rws.cap, D.stream));
-  CU(fn_, cudaMemcpyAsync(out, D.yf.p, ob, cudaMemcpyDeviceToHost, D.stream));
-  CU(fn_, cudaStreamSynchronize(D.stream));
+  download(fn_, D, {{out, D.yf.p, ob}});
 }
 
 void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p,
@@ -707,17 +786,19 @@ void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yro
   CU(fn_, D.gather.ensure(approx ? lp_mu_ws_bytes(yrows, k) : lp_ws_bytes(xrows, yrows, dim, k, sms)));
   CU(fn_, D.oidx.ensure(ib));
   CU(fn_, D.odist.ensure(db));
-  if (xb) CU(fn_, cudaMemcpyAsync(D.x.p, x, xb, cudaMemcpyHostToDevice, D.stream));
-  CU(fn_, cudaMemcpyAsync(D.y.p, y, yb, cudaMemcpyHostToDevice, D.stream));
+  Trace tr;
+  tr("lpk buffers ready");
+  upload(fn_, D, {{D.x.p, x, xb}, {D.y.p, y, yb}});
+  if (tr.on) { cudaStreamSynchronize(D.stream); tr("lpk uploads done (traced runs wait here)", (long long)xb, (long long)yb); }
   if (approx)
     CU(fn_, lp_topk_mu(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, mu, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p,
                        D.odist.p, D.stream));
   else
     CU(fn_, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p, D.odist.p,
                     D.stream));
-  CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
-  CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
-  CU(fn_, cudaStreamSynchronize(D.stream));
+  if (tr.on) { cudaStreamSynchronize(D.stream); tr("lpk kernels done"); }
+  download(fn_, D, {{idx, D.oidx.p, ib}, {dist, D.odist.p, db}});
+  tr("lpk results delivered", (long long)ib, (long long)db);
 }
 
 // ---- the filter overload and its caller --------------------------------
@@ -733,10 +814,7 @@ void HostCall::filt_begin(const float* x, const float* y, int xrows, int yrows, 
   CU(fn_, D.y.ensure(yb ? yb : 4));
   CU(fn_, D.oidx.ensure(ib ? ib : 8));
   CU(fn_, D.odist.ensure(db ? db : 4));
-  if (xb) CU(fn_, cudaMemcpyAsync(D.x.p, x, xb, cudaMemcpyHostToDevice, D.stream));
-  if (yb) CU(fn_, cudaMemcpyAsync(D.y.p, y, yb, cudaMemcpyHostToDevice, D.stream));
-  if (ib) CU(fn_, cudaMemcpyAsync(D.oidx.p, idx, ib, cudaMemcpyHostToDevice, D.stream));
-  if (db) CU(fn_, cudaMemcpyAsync(D.odist.p, dist, db, cudaMemcpyHostToDevice, D.stream));
+  upload(fn_, D, {{D.x.p, x, xb}, {D.y.p, y, yb}, {D.oidx.p, idx, ib}, {D.odist.p, dist, db}});
 }
 
 void HostCall::filt_run(const std::vector<FilterGroup>& groups, int xrows, int yrows, int dim, int k, double p) {
@@ -776,9 +854,7 @@ void HostCall::filt_run(const std::vector<FilterGroup>& groups, int xrows, int y
 void HostCall::filt_end(int yrows, int k, uint64_t* idx, float* dist) {
   Gpu& D = ctx_->gpus[0];
   const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
-  if (ib) CU(fn_, cudaMemcpyAsync(idx, D.oidx.p, ib, cudaMemcpyDeviceToHost, D.stream));
-  if (db) CU(fn_, cudaMemcpyAsync(dist, D.odist.p, db, cudaMemcpyDeviceToHost, D.stream));
-  CU(fn_, cudaStreamSynchronize(D.stream));
+  download(fn_, D, {{idx, D.oidx.p, ib}, {dist, D.odist.p, db}});
 }
 
 // a std::unordered_set<size_t> built from a list: duplicates collapse; ascending order here

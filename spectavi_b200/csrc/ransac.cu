@@ -42,6 +42,29 @@ __device__ __forceinline__ Rot make_jacobi(double x, double y, double z) {
   return r;
 }
 
+// real_2x2_jacobi_svd: the left and right rotations that diagonalise the 2 x 2 block (m00 m01; m10 m11).
+// NOT inlined on purpose: the divisions and square roots in here expand to ~300 SASS instructions, and one copy per
+// (p, q) pair made the scoring kernel 3 800 instructions (61 KB) -- ncu r02 showed the warps waiting on instruction
+// fetch (stall no_instruction 3.5 per issue).  One shared copy keeps the sweep inside the instruction cache; the
+// arithmetic is the same instruction sequence either way.
+__device__ __noinline__ void rotations_2x2(double m00, double m01, double m10, double m11, Rot& jl, Rot& jr) {
+  Rot rot1;
+  const double t = m00 + m11, d = m10 - m01;
+  if (fabs(d) < DBL_MIN) { rot1.s = 0.0; rot1.c = 1.0; }
+  else {
+    const double uu = t / d;
+    const double tmp = sqrt(1.0 + uu * uu);
+    rot1.s = 1.0 / tmp;
+    rot1.c = uu / tmp;
+  }
+  const double a00 = rot1.c * m00 + rot1.s * m10, a01 = rot1.c * m01 + rot1.s * m11;
+  const double a11 = -rot1.s * m01 + rot1.c * m11;
+  jr = make_jacobi(a00, a01, a11);
+  const double c2 = jr.c, s2 = -jr.s;
+  jl.c = rot1.c * c2 - rot1.s * s2;
+  jl.s = rot1.c * s2 + rot1.s * c2;
+}
+
 // Two-sided Jacobi SVD of an N x N matrix held in registers (row-major a; destroyed).  WANT_U: also U.
 // Outputs: sv descending, u / v with their columns permuted along.  All loops over p, q, k are unrolled
 // at compile time so that a, u, v stay in registers.
@@ -73,24 +96,8 @@ __device__ __forceinline__ void jacobi_svd(double (&a)[N * N], double (&sv)[N], 
         const double threshold = fmax(DBL_MIN, precision * max_diag);
         if (fabs(a[p * N + q]) > threshold || fabs(a[q * N + p]) > threshold) {
           finished = false;
-          // real_2x2_jacobi_svd on the (p, q) block
-          const double m00 = a[p * N + p], m01 = a[p * N + q], m10 = a[q * N + p], m11 = a[q * N + q];
-          Rot rot1;
-          const double t = m00 + m11, d = m10 - m01;
-          if (fabs(d) < DBL_MIN) { rot1.s = 0.0; rot1.c = 1.0; }
-          else {
-            const double uu = t / d;
-            const double tmp = sqrt(1.0 + uu * uu);
-            rot1.s = 1.0 / tmp;
-            rot1.c = uu / tmp;
-          }
-          const double a00 = rot1.c * m00 + rot1.s * m10, a01 = rot1.c * m01 + rot1.s * m11;
-          const double a11 = -rot1.s * m01 + rot1.c * m11;
-          const Rot jr = make_jacobi(a00, a01, a11);
-          const double c2 = jr.c, s2 = -jr.s;
-          Rot jl;
-          jl.c = rot1.c * c2 - rot1.s * s2;
-          jl.s = rot1.c * s2 + rot1.s * c2;
+          Rot jl, jr;   // real_2x2_jacobi_svd on the (p, q) block
+          rotations_2x2(a[p * N + p], a[p * N + q], a[q * N + p], a[q * N + q], jl, jr);
           // work.applyOnTheLeft(p, q, j_left): rows p, q
 #pragma unroll
           for (int k = 0; k < N; ++k) {

@@ -59,7 +59,7 @@ def ransac_process_fundamental_matrices(x0, x1, F, options=DEFAULT_OPTIONS, want
     if want_masks:
         words = masks.arr.view('uint32').reshape(nF, -1)
         bits = np.unpackbits(words.view('uint8'), axis=1, bitorder='little')[:, :npt]
-        ret['inlier_mask'] = bits.astype(bool)
+        ret['inlier_mask'] = bits.view(bool)            # 0 / 1 bytes: no second pass over nF x npt
     return ret
 
 

@@ -33,7 +33,10 @@ def run(npt=2000, ntries=4000, cpu_hyps=64):
     opts = {'required_percent_inliers': .6, 'reprojection_error_allowed': 3.35e-4, 'find_best_even_in_failure': False,
             'singular_value_ratio_allowed': 3e-2}
     mvg.ransac_process_fundamental_matrices(x0, x1, F, opts)      # warm-up at full size (scratch buffers grow once)
-    t0 = time.perf_counter(); r = mvg.ransac_process_fundamental_matrices(x0, x1, F, opts); t_e2e = time.perf_counter() - t0
+    t_e2e = t_nomask = 1e30
+    for _ in range(5):
+        t0 = time.perf_counter(); r = mvg.ransac_process_fundamental_matrices(x0, x1, F, opts); t_e2e = min(t_e2e, time.perf_counter() - t0)
+        t0 = time.perf_counter(); mvg.ransac_process_fundamental_matrices(x0, x1, F, opts, want_masks=False); t_nomask = min(t_nomask, time.perf_counter() - t0)
     passed = int(r['ok'].sum())          # hypotheses rejected by the SVD gate cost no DLT solves
     gated = int(sum(mo.essential_cameras(F[i].reshape(3, 3), 3e-2) is not None for i in range(min(nF, 200))))
     # device-resident
@@ -64,7 +67,8 @@ def run(npt=2000, ntries=4000, cpu_hyps=64):
         nvalid = int((~(np.abs(sv[:, 0] - sv[:, 1]) / (np.abs(sv[:, 0] + sv[:, 1]) / 2.) > 3e-2)).sum())
     solves = nvalid * 4 * npt
     out = {"workload": "RANSAC scoring: %d hypotheses (%s pass the SVD gate) x 4 cameras x %d matches" % (nF, nvalid, npt),
-           "gpu_device_ms": ms, "gpu_e2e_ms": t_e2e * 1e3, "dlt_solves": solves, "gpu_G_dlt_solves_per_s": solves / ms / 1e6,
+           "gpu_device_ms": ms, "gpu_e2e_ms": t_e2e * 1e3,
+           "gpu_e2e_ms_without_inlier_masks": t_nomask * 1e3, "dlt_solves": solves, "gpu_G_dlt_solves_per_s": solves / ms / 1e6,
            "hypotheses_per_s": nF / ms * 1e3, "accepted_hypotheses": passed, "first_200_gated_in": gated}
     if mo.have_ref():
         cores = os.cpu_count() or 1
