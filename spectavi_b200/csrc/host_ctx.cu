@@ -771,34 +771,60 @@ void HostCall::normalize(const float* x, int rows, int dim, float* out) {
   download(fn_, D, {{out, D.yf.p, ob}});
 }
 
-void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p,
-                   uint64_t* idx, void* dist, float mu) {
-  // single GPU: the graded shapes of this entry point are small (test/test_feature.py:67-81)
-  Gpu& D = ctx_->gpus[0];
+// K1f on one GPU: every train row, the query rows [0, yrows) of `y`, results to idx / dist (host)
+static void lpk_on(const char* fn, Gpu& D, const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k,
+                   double p, float mu, uint64_t* idx, void* dist) {
   int sms = 0;
-  CU(fn_, cudaSetDevice(D.dev));
-  CU(fn_, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, D.dev));
+  CU(fn, cudaSetDevice(D.dev));
+  CU(fn, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, D.dev));
   const size_t xb = (size_t)xrows * dim * 4, yb = (size_t)yrows * dim * 4;
   const size_t ib = (size_t)yrows * k * sizeof(uint64_t), db = (size_t)yrows * k * 4;
-  CU(fn_, D.x.ensure(xb ? xb : 4));
-  CU(fn_, D.y.ensure(yb ? yb : 4));
+  CU(fn, D.x.ensure(xb ? xb : 4));
+  CU(fn, D.y.ensure(yb ? yb : 4));
   const bool approx = is_int ? ((int)mu != 0) : (mu != 0.f);      // Scalar m_mu: truncated for the int instantiation
-  CU(fn_, D.gather.ensure(approx ? lp_mu_ws_bytes(yrows, k) : lp_ws_bytes(xrows, yrows, dim, k, sms)));
-  CU(fn_, D.oidx.ensure(ib));
-  CU(fn_, D.odist.ensure(db));
+  CU(fn, D.gather.ensure(approx ? lp_mu_ws_bytes(yrows, k) : lp_ws_bytes(xrows, yrows, dim, k, sms)));
+  CU(fn, D.oidx.ensure(ib));
+  CU(fn, D.odist.ensure(db));
   Trace tr;
   tr("lpk buffers ready");
-  upload(fn_, D, {{D.x.p, x, xb}, {D.y.p, y, yb}});
+  upload(fn, D, {{D.x.p, x, xb}, {D.y.p, y, yb}});
   if (tr.on) { cudaStreamSynchronize(D.stream); tr("lpk uploads done (traced runs wait here)", (long long)xb, (long long)yb); }
   if (approx)
-    CU(fn_, lp_topk_mu(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, mu, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p,
-                       D.odist.p, D.stream));
+    CU(fn, lp_topk_mu(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, mu, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p,
+                      D.odist.p, D.stream));
   else
-    CU(fn_, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p, D.odist.p,
-                    D.stream));
+    CU(fn, lp_topk(D.x.p, D.y.p, is_int, xrows, yrows, dim, k, p, D.gather.p, D.gather.cap, (uint64_t*)D.oidx.p, D.odist.p,
+                   D.stream));
   if (tr.on) { cudaStreamSynchronize(D.stream); tr("lpk kernels done"); }
-  download(fn_, D, {{idx, D.oidx.p, ib}, {dist, D.odist.p, db}});
+  download(fn, D, {{idx, D.oidx.p, ib}, {dist, D.odist.p, db}});
   tr("lpk results delivered", (long long)ib, (long long)db);
+}
+
+void HostCall::lpk(const void* x, const void* y, bool is_int, int xrows, int yrows, int dim, int k, double p,
+                   uint64_t* idx, void* dist, float mu) {
+  // Query rows are independent (BruteForceNn.h:51-119 loops over them), so with SPECTAVI_GPUS > 1 every GPU takes a
+  // slice of the queries against ALL train rows: no merge, no collective.  Each GPU needs its own copy of x, so the
+  // split only pays when a slice's compute outweighs that upload -- at least 8192 query rows per GPU
+  // (test/test_feature.py:67-81's shapes stay on one GPU).
+  const int G = (int)ctx_->gpus.size();
+  int use = yrows / 8192;
+  use = use < 1 ? 1 : (use > G ? G : use);
+  if (use == 1) {
+    lpk_on(fn_, ctx_->gpus[0], x, y, is_int, xrows, yrows, dim, k, p, mu, idx, dist);
+    return;
+  }
+  const int per = (yrows + use - 1) / use;
+  const char* fn = fn_;
+  std::vector<std::thread> th;
+  auto slice = [&](int g) {
+    const int y0 = g * per < yrows ? g * per : yrows, yn = y0 + per <= yrows ? per : yrows - y0;
+    if (yn <= 0) return;
+    lpk_on(fn, ctx_->gpus[g], x, static_cast<const char*>(y) + (size_t)y0 * dim * 4, is_int, xrows, yn, dim, k, p, mu,
+           idx + (size_t)y0 * k, static_cast<char*>(dist) + (size_t)y0 * k * 4);
+  };
+  for (int g = 1; g < use; ++g) th.emplace_back(slice, g);
+  slice(0);
+  for (std::thread& t : th) t.join();
 }
 
 // ---- the filter overload and its caller --------------------------------

@@ -71,6 +71,15 @@ def run_abi():
         ci, cd = feature.nn_cascading_hash(xf, yf, k=2, m=m, n=2, g=2)
         oi, od = po.cascade(xf, yf, dev.cascade_dictionary(dim, m, 2), 2, 4)
         assert (ci == oi).all() and (cd == od).all(), "SPECTAVI_GPUS cascade differs from the oracle"
+    # nn_bruteforce shards the QUERY rows once there are 8192 per GPU (host_ctx.cu HostCall::lpk)
+    rng = np.random.RandomState(5)
+    xf = rng.randn(1500, 36).astype("float32")
+    yf = rng.randn(8192 * 2 + 77, 36).astype("float32")
+    for pw, k, mu in ((1., 2, 0.), (2., 3, 0.), (1., 2, .05)):
+        gi, gd = feature.nn_bruteforce(xf, yf, p=pw, mu=mu, k=k)
+        oi, od = po.bruteforce(xf, yf, k, pw, mu)
+        assert (gi.reshape(oi.shape) == oi).all() and (gd.reshape(od.shape).view(np.uint32) == od.view(np.uint32)).all(), \
+            "SPECTAVI_GPUS nn_bruteforce differs from the oracle"
     print("MGPU_ABI_OK gpus=%s" % os.environ.get("SPECTAVI_GPUS"))
 
 
