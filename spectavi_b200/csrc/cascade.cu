@@ -473,15 +473,19 @@ __global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __gri
   const int ntiles = (P.rows + HP_ROWS - 1) / HP_ROWS;
   const int my_tiles = blockIdx.x < ntiles ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
+  // The producer warp never touches sB / sCol, so it takes no part in the per-group barriers: its first row tiles
+  // are in flight while the other nine warps are still fetching the B operand, and it runs ahead across groups,
+  // held back only by the ring's empty barriers.
+  constexpr int HQ_WORKERS = HQ_THREADS - 32;
   for (int grp = 0; grp < P.groups; ++grp) {
-    {   // B operand and column constants of this group of tables
+    if (warp != 0) {   // B operand and column constants of this group of tables
       const uint4* src = reinterpret_cast<const uint4*>(P.img + (size_t)grp * dim * N);
       uint4* dst = reinterpret_cast<uint4*>(sB);
-      for (int e = tid; e < dim * N / 16; e += HQ_THREADS) dst[e] = src[e];
-      for (int e = tid; e < N; e += HQ_THREADS) sCol[e] = P.colsum[grp * N + e];
+      for (int e = tid - 32; e < dim * N / 16; e += HQ_WORKERS) dst[e] = src[e];
+      for (int e = tid - 32; e < N; e += HQ_WORKERS) sCol[e] = P.colsum[grp * N + e];
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(HQ_WORKERS) : "memory");
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncthreads();
     const uint32_t it0 = (uint32_t)grp * (uint32_t)my_tiles;   // the same iteration count in every role
     if (warp == 0) {
       if (lane == 0)
@@ -541,7 +545,8 @@ __global__ void __launch_bounds__(HQ_THREADS) hash_project_i8_kernel(const __gri
         mbar_arrive(bar_tempty + 8 * a);
       }
     }
-    __syncthreads();   // every tile of the group is through its epilogue, hence through its MMAs: sB is free
+    // every tile of the group is through its epilogue, hence through its MMAs: sB is free
+    if (warp != 0) asm volatile("bar.sync 1, %0;" ::"n"(HQ_WORKERS) : "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
