@@ -24,6 +24,7 @@
 #include "spv_common.h"
 
 #include <cuda_bf16.h>
+#include <climits>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -647,6 +648,7 @@ __global__ void bucket_scatter_kernel(const int32_t* __restrict__ codes, size_t 
 // ---------------------------------------------------------------- K4
 constexpr int PR_WARPS = 4;      // warps per CTA
 constexpr int PR_QPW = 4;        // query rows per warp (one per 8-lane group)
+constexpr int PR_PAD = INT_MIN;  // a list slot that holds no candidate: negative, and `& INT_MAX` is row 0
 constexpr int PR_LCAP = 256;     // candidate ids staged per query before a distance pass (multiple of 8)
 
 struct PrParams {
@@ -699,17 +701,17 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
   static_assert(NQ == 16, "the rank computation below takes two slots per lane of an 8-lane group");
   __shared__ __align__(16) int32_t lists[PR_WARPS][PR_QPW][PR_LCAP];
   __shared__ int Tq[NQ], order[NQ], ovf;
+  __shared__ __align__(16) int32_t padv[8];             // eight PR_PADs: what a group with no ids left reads in a drain step
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = lane >> 3, l8 = lane & 7;
   const long long first = ((long long)blockIdx.x * PR_WARPS + warp) * PR_QPW;
   const int P_total = P.n << P.nb;   // probe codes of a query: n tables x 2^nb settings
   // With at most 8 probe codes (one chunk) the whole candidate list of a query is known before the first
   // gather, and the CTA's 16 lists can be dealt out again by length (below); CTA-uniform.
   const bool balanced = P_total <= 8;
+  if (threadIdx.x == 0) ovf = 0;
+  if (threadIdx.x < 8) padv[threadIdx.x] = PR_PAD;
+  __syncthreads();
   if (!balanced && first >= P.yrows) return;   // whole warp
-  if (balanced) {
-    if (threadIdx.x == 0) ovf = 0;
-    __syncthreads();
-  }
   bool live = first + q < P.yrows;
   int r = live ? (int)(first + q) : P.yrows - 1;   // a dead group shadows the last row and offers nothing
   const unsigned FULL = 0xFFFFFFFFu;
@@ -730,36 +732,38 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
   int listn = 0;                                     // ids staged for this group's query
 
   auto drain = [&]() {
-    if ((listn & 7) && l8 >= (listn & 7)) list[(listn & ~7) + l8] = -1;   // pad the last step
+    if ((listn & 7) && l8 >= (listn & 7)) list[(listn & ~7) + l8] = PR_PAD;   // pad the last step
     __syncwarp();
     const int nmax = __reduce_max_sync(FULL, listn);
     for (int c0 = 0; c0 < nmax; c0 += 8) {
-      int4 ia = make_int4(-1, -1, -1, -1), ib = ia;
-      int own = -1;                       // the candidate whose distance ends up in this lane
-      if (c0 < listn) {
-        ia = *reinterpret_cast<const int4*>(list + c0);
-        ib = *reinterpret_cast<const int4*>(list + c0 + 4);
-        own = list[c0 + l8];
-      }
-      const int id[8] = {ia.x, ia.y, ia.z, ia.w, ib.x, ib.y, ib.z, ib.w};
+      // a group whose list is exhausted reads eight pads instead: one address select, no predicated loads
+      const int32_t* src = c0 < listn ? list + c0 : padv;
+      const int4 ia = *reinterpret_cast<const int4*>(src), ib = *reinterpret_cast<const int4*>(src + 4);
+      const int own = src[l8];            // the candidate whose distance ends up in this lane
+      // A slot without a candidate (PR_PAD) gathers row 0 instead of being predicated off: its distance is never
+      // looked at (`own < 0` makes the key KEY_NONE below), row 0 stays in L1, and the step loses 8 predicates and the
+      // 32 register moves that gave the skipped loads a value (SASS: 145 -> ~125 instructions per step).  The mask is
+      // a LOP3; max(id, 0) would be a VIMNMX, which issues at a third of the rate (pipe_peak.cu).
+      const uint32_t id[8] = {(uint32_t)ia.x & 0x7FFFFFFFu, (uint32_t)ia.y & 0x7FFFFFFFu, (uint32_t)ia.z & 0x7FFFFFFFu,
+                              (uint32_t)ia.w & 0x7FFFFFFFu, (uint32_t)ib.x & 0x7FFFFFFFu, (uint32_t)ib.y & 0x7FFFFFFFu,
+                              (uint32_t)ib.z & 0x7FFFFFFFu, (uint32_t)ib.w & 0x7FFFFFFFu};
       uint32_t d[8];
 #pragma unroll
       for (int u = 0; u < 8; ++u) d[u] = 0;
 #pragma unroll
       for (int c = 0; c < nch; ++c) {
-        uint4 yc;
-        if (NCH > 0) yc = yv[NCH > 0 ? c : 0];
-        else yc = (l8 + 8 * c < nk16) ? __ldg(yrow + l8 + 8 * c) : make_uint4(0, 0, 0, 0);
-        uint4 v[8];
+        if (l8 + 8 * c < nk16) {          // this lane holds a 16-byte slice of chunk c (all lanes when dim % 128 == 0)
+          const uint4 yc = NCH > 0 ? yv[NCH > 0 ? c : 0] : __ldg(yrow + l8 + 8 * c);
+          const uint4* xs = reinterpret_cast<const uint4*>(P.xu8) + l8 + 8 * c;
+          uint4 v[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-          v[u] = (id[u] >= 0 && l8 + 8 * c < nk16)
-                     ? __ldg(reinterpret_cast<const uint4*>(P.xu8 + (size_t)id[u] * P.dim) + l8 + 8 * c)
-                     : yc;   // |y - y| = 0
+          for (int u = 0; u < 8; ++u)     // 32 x 32 -> 64-bit product: one IMAD.WIDE
+            v[u] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(xs) + (unsigned long long)id[u] * (uint32_t)P.dim));
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          d[u] = sad4(v[u].x, yc.x, d[u]); d[u] = sad4(v[u].y, yc.y, d[u]);
-          d[u] = sad4(v[u].z, yc.z, d[u]); d[u] = sad4(v[u].w, yc.w, d[u]);
+          for (int u = 0; u < 8; ++u) {
+            d[u] = sad4(v[u].x, yc.x, d[u]); d[u] = sad4(v[u].y, yc.y, d[u]);
+            d[u] = sad4(v[u].z, yc.z, d[u]); d[u] = sad4(v[u].w, yc.w, d[u]);
+          }
         }
       }
       // transposed butterfly over the 8 lanes of the group: lane l8 ends with sum_lanes d[l8]
@@ -841,7 +845,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
         if (verify) { s_code = __shfl_sync(FULL, code, pp, 8); s_t = __shfl_sync(FULL, t, pp, 8); }   // warp-uniform branch
         if ((uint32_t)l8 < b_len[pp]) {
           int id = idv[pp];
-          if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = -1;
+          if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = PR_PAD;
           list[listn + b_excl[pp] + l8] = id;
         }
       }
@@ -856,7 +860,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
             const uint32_t k = k0 + l8;
             if (k < b_len[pp]) {
               int id = __ldg(P.ids + b_start[pp] + k);
-              if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = -1;
+              if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = PR_PAD;
               list[listn + b_excl[pp] + k] = id;
             }
           }
@@ -908,7 +912,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32, NCH == 1 ? 8 : 4) probe_rerank_
         if (verify) { s_code = __shfl_sync(FULL, code, pos, 8); s_t = __shfl_sync(FULL, t, pos, 8); }
         if (f0 + l8 < take) {
           int id = __ldg(P.ids + s_start + (f - s_excl));
-          if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = -1;
+          if (verify && (uint32_t)__ldg(P.xcodes + (size_t)s_t * P.xrows + id) != s_code) id = PR_PAD;
           list[listn + f0 + l8] = id;
         }
       }
