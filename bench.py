@@ -271,6 +271,33 @@ def pipe_peak(dev_index):
     return {names[v].decode(): {"ops_per_clk_sm": out[2 * v], "gops": out[2 * v + 1]} for v in range(n)}
 
 
+def k1f_query_sharded(world, device):
+    """nn_bruteforce through the C ABI with SPECTAVI_GPUS=world (already set for this process): the query rows are split
+    over the GPUs, every GPU holds all train rows, no exchange (host_ctx.cu HostCall::lpk).  Beside it: the same problem
+    device-resident on ONE GPU (CUDA events), and equality of the two results."""
+    import torch
+    from spectavi_b200 import device as dev
+    from spectavi_b200 import feature
+    rows = 8192 * world
+    rng = np.random.RandomState(4)
+    x = rng.randn(rows, 132).astype("float32"); y = rng.randn(rows, 132).astype("float32")
+    feature.nn_bruteforce(x, y, p=1., mu=0., k=2)
+    best = 1e30
+    for _ in range(3):
+        t0 = time.perf_counter(); gi, gd = feature.nn_bruteforce(x, y, p=1., mu=0., k=2); best = min(best, time.perf_counter() - t0)
+    dx, dy = torch.from_numpy(x).to(device), torch.from_numpy(y).to(device)
+    dev.nn_bruteforce(dx, dy, p=1., k=2)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); di, dd = dev.nn_bruteforce(dx, dy, p=1., k=2); e1.record(); torch.cuda.synchronize()
+    one = e0.elapsed_time(e1)
+    return {"workload": "nn_bruteforce %d x %d x 132 float32, p=1, k=2" % (rows, rows), "gpus": world,
+            "e2e_ms(C ABI, pageable numpy, query rows sharded)": best * 1e3, "Gpairs_per_s_e2e": rows * rows / best / 1e9,
+            "one_gpu_device_resident_ms": one, "speedup_vs_one_gpu_device_resident": one / (best * 1e3),
+            "equals_one_gpu_result": bool((gi.reshape(rows, 2) == di.cpu().numpy().view(np.uint64).reshape(rows, 2)).all()
+                                          and (gd.reshape(rows, 2) == dd.cpu().numpy().reshape(rows, 2)).all())}
+
+
 def guarded(out, key, fn):
     """A side measurement must never cost the bench line."""
     try:
@@ -639,6 +666,7 @@ def run_b200(args):
             extras["c_abi_mgpu"] = dict(c_abi, note="timed as the e2e figure of this line")
             if c5_sharded is not None:
                 extras["c5_cascade_sharded"] = c5_sharded
+            guarded(extras, "k1f_query_sharded", lambda: k1f_query_sharded(world, device))
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3) if args.warmup else 0, "ms_per_step": step_ms / args.steps,

@@ -58,6 +58,17 @@ def test_bruteforce_bit_exact_vs_oracle(po, feature, shape, p, k):
     assert (gd.reshape(od.shape).view(np.uint32) == od.view(np.uint32)).all()
 
 
+def test_bruteforce_staged_upload_path(po, feature):
+    # more than 1 MB of input: the rows go up through the upload lanes (host_ctx.cu upload()), cut at 256 KB grains that
+    # fall inside rows and across the x / y boundary
+    rng = np.random.RandomState(77)
+    x = rng.randn(3001, 132).astype("float32")
+    y = rng.randn(2503, 132).astype("float32")
+    gi, gd = feature.nn_bruteforce(x, y, p=1., mu=0., k=2)
+    oi, od = po.bruteforce(x, y, 2, 1., 0.)
+    assert (gi == oi).all() and (gd.view(np.uint32) == od.view(np.uint32)).all()
+
+
 def test_bruteforce_fewer_rows_than_k(po, feature):
     # BruteForceNn.h:111-118 writes back to front: 3 neighbours of k=5 land in columns 2..4
     rng = np.random.RandomState(3)
