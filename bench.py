@@ -275,10 +275,11 @@ def k1f_query_sharded(world, device):
     """nn_bruteforce through the C ABI with SPECTAVI_GPUS=world (already set for this process): the query rows are split
     over the GPUs, every GPU holds all train rows, no exchange (host_ctx.cu HostCall::lpk).  Beside it: the same problem
     device-resident on ONE GPU (CUDA events), and equality of the two results."""
+    import numpy as np
     import torch
     from spectavi_b200 import device as dev
     from spectavi_b200 import feature
-    rows = 8192 * world
+    rows = 16384 * world
     rng = np.random.RandomState(4)
     x = rng.randn(rows, 132).astype("float32"); y = rng.randn(rows, 132).astype("float32")
     feature.nn_bruteforce(x, y, p=1., mu=0., k=2)

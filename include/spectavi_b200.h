@@ -48,7 +48,13 @@ struct NdArray {
 };
 typedef struct NdArray NdArray;
 
-/* ============================ Part 1: drop-in entry points (host pointers) */
+/* ============================ Part 1: drop-in entry points (host pointers)
+ * Host arrays are ordinary pageable memory; the library stages them itself.  Environment:
+ *   SPECTAVI_GPUS=N|all       nn_bruteforcel1k2 / nn_cascading_hash shard the TRAIN rows over N GPUs (NCCL all-gather
+ *                             of the per-GPU top-2 keys); nn_bruteforce / nn_bruteforcei shard the QUERY rows (from
+ *                             8192 rows per GPU, no exchange).  Results are bit-identical to one GPU.
+ *   SPECTAVI_UPLOAD_LANES=1..8  host threads staging a large pageable array (default 4)
+ *   SPECTAVI_SEED=<uint>      seed of the cascade's hyperplane dictionary */
 
 /* replaces src/Spectavi.cpp:284-298 (BruteForceNnL1K2, src/BruteForceNnL1K2.h).
  * x: xrows x dim uint8 train rows, y: yrows x dim uint8 query rows, row-major,
