@@ -182,6 +182,19 @@ size_t spv_ratio_ws_bytes(int yrows);
 int spv_ratio_matches_device(const uint64_t *dkeys, int yrows, double min_ratio, int dist_is_f32, uint8_t *dmask,
                              uint64_t *dmatches, uint32_t *dcount, void *dws, size_t ws_bytes, void *stream);
 
+/* K6 without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and results as spv_ratio_matches_device, but the per-block scratch is a file-scope device array
+ * inside the library (65 540 bytes on every GPU that loads it, until exit) instead of a caller workspace, and the call
+ * makes no cudaMalloc / cudaFree.  Limit: yrows <= spv_ratio_static_max_rows() = 4 194 304; beyond it the call returns
+ * -1 with a message in spv_last_error() and launches nothing.  The array belongs to the CURRENT device and is shared
+ * by all calls on it: calls that overlap on the GPU (different streams, different threads) race -- keep them on one
+ * stream or order them yourself.  The first call on a device looks the array's address up (cudaGetSymbolAddress);
+ * make one call before starting a graph capture. */
+int spv_ratio_static_max_rows(void);
+int spv_ratio_matches_device_static(const uint64_t *dkeys, int yrows, double min_ratio, int dist_is_f32, uint8_t *dmask,
+                                    uint64_t *dmatches, uint32_t *dcount, void *stream);
+
 /* K7: the quantiser on device rows.  dout_f32 and / or dout_u8 (= value + 128, what the matchers take;
  * either may be NULL): rows x spv_normalize_new_dim(dim). */
 size_t spv_normalize_ws_bytes(int dim);

@@ -106,6 +106,19 @@ int spv_ratio_matches_device(const uint64_t* dkeys, int yrows, double min_ratio,
   return 0;
 }
 
+int spv_ratio_static_max_rows(void) { return ratio_static_max_rows(); }
+
+int spv_ratio_matches_device_static(const uint64_t* dkeys, int yrows, double min_ratio, int dist_is_f32, uint8_t* dmask,
+                                    uint64_t* dmatches, uint32_t* dcount, void* stream) {
+  if (yrows < 0) return fail("negative row count");
+  if (yrows > ratio_static_max_rows())
+    return fail("spv_ratio_matches_device_static: yrows = %d exceeds the built-in scratch (%d rows); use "
+                "spv_ratio_matches_device with a workspace", yrows, ratio_static_max_rows());
+  CU_OR_FAIL(ratio_matches_static(reinterpret_cast<const unsigned long long*>(dkeys), yrows, min_ratio, dist_is_f32 != 0,
+                                  dmask, dmatches, dcount, (cudaStream_t)stream));
+  return 0;
+}
+
 size_t spv_normalize_ws_bytes(int dim) { return normalize_ws_bytes(dim); }
 int spv_normalize_new_dim(int dim) { return normalize_new_dim(dim); }
 

@@ -15,6 +15,8 @@
 // match): per-block pass counts, one-block exclusive scan of the counts, scatter.
 #include "spv_common.h"
 
+#include <mutex>
+
 namespace spv {
 namespace {
 
@@ -132,6 +134,44 @@ cudaError_t ratio_matches(const unsigned long long* keys, int yrows, double min_
   ratio_scatter_kernel<<<nblocks, RT_THREADS, 0, stream>>>(keys, yrows, min_ratio, dist_f32 ? 1 : 0, bc, matches);
   count_launch(3);
   return cudaGetLastError();
+}
+
+// ---- the variant that allocates nothing (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).  The per-block counts
+// live in a file-scope device array instead of a caller-supplied workspace: RATIO_STATIC_MAX_ROWS query rows at most,
+// (2^22 / 256 + 1) * 4 B = 65 540 B, held by every GPU that loads the library until the process exits.  Every call on
+// a GPU shares the array, so calls that overlap on that GPU (different streams) race; calls on one stream are ordered.
+// Nothing in it has to start at zero: ratio_count_kernel writes every entry the other two kernels read.
+constexpr int RATIO_STATIC_MAX_ROWS = 1 << 22;
+static __device__ __align__(256) unsigned g_ratio_static_counts[RATIO_STATIC_MAX_ROWS / RT_THREADS + 1];
+
+int ratio_static_max_rows() { return RATIO_STATIC_MAX_ROWS; }
+
+cudaError_t ratio_matches_static(const unsigned long long* keys, int yrows, double min_ratio, bool dist_f32,
+                                 unsigned char* mask, uint64_t* matches, unsigned* count, cudaStream_t stream) {
+  if (yrows > RATIO_STATIC_MAX_ROWS) return cudaErrorInvalidValue;
+  // In host code the array's NAME is a host-side stand-in, not a device address: the address is asked for once per
+  // device, with that device current (the first call on a device is the set-up; it allocates nothing either, but a
+  // caller that captures a graph should make one call before the capture starts).
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static unsigned* addr[MAX_DEV] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= MAX_DEV) return cudaErrorInvalidDevice;
+  unsigned* bc;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[dev]) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_ratio_static_counts);
+      if (e != cudaSuccess) return e;
+      addr[dev] = static_cast<unsigned*>(p);
+    }
+    bc = addr[dev];
+  }
+  return ratio_matches(keys, yrows, min_ratio, dist_f32, mask, matches, count, bc, sizeof(g_ratio_static_counts), stream);
 }
 
 }  // namespace spv

@@ -97,6 +97,10 @@ cudaError_t hash_codes(const uint8_t* drows, int rows, int dim, int m, int n, in
 size_t ratio_ws_bytes(int yrows);
 cudaError_t ratio_matches(const unsigned long long* keys, int yrows, double min_ratio, bool dist_f32, unsigned char* mask,
                           uint64_t* matches, unsigned* count, void* ws, size_t ws_bytes, cudaStream_t stream);
+// the same with the scratch in a file-scope device array (no workspace, nothing allocated); yrows <= ratio_static_max_rows()
+int ratio_static_max_rows();
+cudaError_t ratio_matches_static(const unsigned long long* keys, int yrows, double min_ratio, bool dist_f32,
+                                 unsigned char* mask, uint64_t* matches, unsigned* count, cudaStream_t stream);
 // ---- quantize.cu : K7, normalize_to_ubyte_and_multiple_16_dim (spectavi/feature.py:384-407) on the device.
 // dx: rows x dim float32; outputs rows x normalize_new_dim(dim): float32 (nullable) and / or uint8 = value + 128
 // (nullable); ws: normalize_ws_bytes(dim) scratch.
