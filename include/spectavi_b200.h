@@ -54,6 +54,8 @@ typedef struct NdArray NdArray;
  *                             of the per-GPU top-2 keys); nn_bruteforce / nn_bruteforcei shard the QUERY rows (from
  *                             8192 rows per GPU, no exchange).  Results are bit-identical to one GPU.
  *   SPECTAVI_UPLOAD_LANES=1..8  host threads staging a large pageable array (default 4)
+ *   SPECTAVI_CVT_LANES=1..16  host threads converting nn_cascading_hash's float32 rows to uint8 while staging them
+ *                             (default: 3/4 of the host's cores); SPECTAVI_CVT=device converts on the GPU (K0) instead
  *   SPECTAVI_SEED=<uint>      seed of the cascade's hyperplane dictionary */
 
 /* replaces src/Spectavi.cpp:284-298 (BruteForceNnL1K2, src/BruteForceNnL1K2.h).
@@ -214,6 +216,10 @@ int spv_nn_bruteforce_device(const void *dx, const void *dy, int is_int, int xro
 
 /* K0: (uint8)((int)v + 128), the cast of CascadingHashNn.h:236-239 (count % 4 == 0) */
 int spv_f32_to_u8_device(const float *din, uint8_t *dout, size_t count, void *stream);
+/* the same conversion on HOST arrays (any count): what nn_cascading_hash's staging threads apply to the caller's
+ * float32 rows on their way into pinned memory, so that 1 byte per element crosses PCIe instead of 4; results equal
+ * K0's bit for bit, including NaN, +-inf and out-of-range values (the device conversion saturates) */
+void spv_f32_to_u8_host(const float *in, uint8_t *out, size_t count);
 /* scratch bytes spv_cascade_device needs (0 = unsupported parameters) */
 size_t spv_cascade_ws_bytes(int xrows, int yrows, int dim, int m, int n, int g);
 /* K2-K4: cascade-of-hashes match of uint8 (value + 128) query rows dyu8 against

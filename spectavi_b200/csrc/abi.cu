@@ -156,6 +156,8 @@ int spv_nn_bruteforce_device(const void* dx, const void* dy, int is_int, int xro
   return 0;
 }
 
+void spv_f32_to_u8_host(const float* in, uint8_t* out, size_t count) { f32_to_u8_host(in, out, count); }
+
 int spv_f32_to_u8_device(const float* din, uint8_t* dout, size_t count, void* stream) {
   CU_OR_FAIL(f32_to_u8(din, dout, count, (cudaStream_t)stream));
   return 0;

@@ -53,7 +53,7 @@ struct PinBuf {
 // memcpy) -> device (DMA); with two buffers the memcpy of sub-chunk i + 1 runs under the DMA of sub-chunk i,
 // and -- because the DMA sits on its own stream -- under whatever the compute stream is doing.
 constexpr size_t LANE_BYTES = (size_t)4 << 20;
-constexpr int NLANE = 8;                       // lanes that exist; upload_lanes() says how many a float upload uses
+constexpr int NLANE = 16;                      // lanes a context can have; they are created on first use (lanes_init)
 struct Lane {
   cudaStream_t copy = nullptr;
   void* pin[2] = {nullptr, nullptr};
@@ -67,7 +67,7 @@ struct Gpu {
   int dev = -1;
   cudaStream_t stream = nullptr;
   Lane lane[NLANE];
-  bool lanes_ready = false;
+  int lanes_ready = 0;          // lanes [0, lanes_ready) exist
   cudaEvent_t ev[16] = {};      // scratch events (per-chunk completion of the final pass)
   Buf x, y, keys, gather, oidx, odist, xf, yf, dict, ws, rws, sel;
   PinBuf res;
@@ -108,6 +108,29 @@ struct Ctx {
   PinBuf ypin;                     // multi-GPU: the query rows staged ONCE (portable pinned memory), DMA'd by every GPU
   SpinBarrier bar;
 };
+
+// ---- K0 on the host (see upload_f32_as_u8 below) ----
+void f32_to_u8_avx2(const float* s, uint8_t* d, size_t n);   // host_cvt.cu (compiled with -mavx2)
+
+static inline uint8_t f32_to_u8_one(float v) {
+  // cvt.rzi.s32.f32: NaN -> 0, saturating; then + 128 in wrapping arithmetic, low byte
+  int32_t i;
+  if (!(v == v)) i = 0;
+  else if (v >= 2147483648.0f) i = INT32_MAX;
+  else if (v <= -2147483648.0f) i = INT32_MIN;
+  else i = (int32_t)v;
+  return (uint8_t)(((uint32_t)i + 128u) & 0xFFu);
+}
+
+void f32_to_u8_host(const float* s, uint8_t* d, size_t n) {
+  static const bool avx2 = __builtin_cpu_supports("avx2");
+  size_t done = 0;
+  if (avx2) {
+    done = n & ~(size_t)31;
+    f32_to_u8_avx2(s, d, done);
+  }
+  for (size_t i = done; i < n; ++i) d[i] = f32_to_u8_one(s[i]);
+}
 
 namespace {
 
@@ -200,9 +223,12 @@ struct Trace {
 };
 
 // ---- staged uploads ------------------------------------------------------------------------------------
-void lanes_init(const char* fn, Gpu& D) {
-  if (D.lanes_ready) return;
-  for (Lane& L : D.lane) {
+void lanes_init(const char* fn, Gpu& D, int n = 8) {
+  if (D.lanes_ready >= n) return;
+  if (D.lanes_ready == 0)
+    for (cudaEvent_t& e : D.ev) CU(fn, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (int li = D.lanes_ready; li < n && li < NLANE; ++li) {
+    Lane& L = D.lane[li];
     CU(fn, cudaStreamCreateWithFlags(&L.copy, cudaStreamNonBlocking));
     for (int b = 0; b < 2; ++b) {
       CU(fn, cudaHostAlloc(&L.pin[b], LANE_BYTES, cudaHostAllocDefault));
@@ -210,8 +236,7 @@ void lanes_init(const char* fn, Gpu& D) {
     }
     CU(fn, cudaEventCreateWithFlags(&L.ready, cudaEventDisableTiming));
   }
-  for (cudaEvent_t& e : D.ev) CU(fn, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-  D.lanes_ready = true;
+  D.lanes_ready = n < NLANE ? n : NLANE;
 }
 
 // pageable host -> device through the lane's pinned buffers; returns once the last sub-chunk is QUEUED.
@@ -371,21 +396,40 @@ int upload_lanes() {
   static const int n = [] {
     const char* e = getenv("SPECTAVI_UPLOAD_LANES");
     int v = e ? atoi(e) : 4;
-    return v < 1 ? 1 : (v > NLANE ? NLANE : v);
+    return v < 1 ? 1 : (v > 8 ? 8 : v);
   }();
   return n;
 }
 
-// float32 rows -> device uint8 (value + 128): upload through `nl` lanes in parallel (each lane streams a
-// contiguous slice of the rows with its own host thread, so the pageable -> pinned memcpy -- the slow half of
-// the path -- runs nl-wide), K0 converts each sub-chunk on the lane's stream as it lands
-// (CascadingHashNn.h:236-239), and the compute stream waits for every lane.  dtmp: NLANE * 2 * LANE_BYTES of scratch.
-void upload_f32_as_u8(const char* fn, Gpu& D, const float* src, size_t count, uint8_t* dst, float* dtmp) {
-  lanes_init(fn, D);
-  const size_t per_chunk = LANE_BYTES / 4;                     // floats per sub-chunk
+// ---- float32 rows -> device uint8 (value + 128), the cascade's inputs (CascadingHashNn.h:236-239) ----------------
+// The rows have to pass through the CPU anyway (pageable -> pinned), so the conversion happens THERE: a lane's thread
+// reads 4 bytes per element and writes 1 into its pinned buffer, and 1 byte per element crosses PCIe -- against 4 read,
+// 4 written, 4 sent when the floats are staged as they are and K0 converts on the device.  Measured on the box
+// (tools/ubench_stage_cvt.cu, 512 MB of floats): staged as floats 12.0 ms at best (4-8 threads, 45 GB/s: the host's
+// memory system is the limit); converted while staged 11.6 / 8.0 / 6.4 ms with 4 / 6 / 8 threads (84 GB/s of floats) --
+// it scales with the threads because each one moves 2.5x fewer bytes.  Semantics are K0's, bit for bit
+// (f32_to_u8_host below; tests/test_f32_to_u8_host.py).  SPECTAVI_CVT=device keeps the old path (A/B runs).
+// threads of one converting upload: SPECTAVI_CVT_LANES (1 .. NLANE), default 3/4 of the host's cores within [4, NLANE],
+// shared between the GPUs of a call.  C5 end to end on the 16-core box (tools/bench_e2e_cvt.py): K0 on the device
+// 28.8 ms; converted while staged 31.9 / 20.0 / 18.3 / 17.8 ms with 4 / 8 / 12 / 16 threads.
+int cvt_lanes(int gpus) {
+  static const int n = [] {
+    const char* e = getenv("SPECTAVI_CVT_LANES");
+    int v = e ? atoi(e) : (int)(std::thread::hardware_concurrency() * 3 / 4);
+    if (!e && v < 4) v = 4;
+    return v < 1 ? 1 : (v > NLANE ? NLANE : v);
+  }();
+  const int per = n / (gpus > 0 ? gpus : 1);
+  return per < 2 ? 2 : per;
+}
+
+void upload_f32_as_u8(const char* fn, Gpu& D, const float* src, size_t count, uint8_t* dst, float* dtmp, int gpus) {
+  static const bool on_device = [] { const char* e = getenv("SPECTAVI_CVT"); return e && !strcmp(e, "device"); }();
+  const size_t per_chunk = on_device ? LANE_BYTES / 4 : ((size_t)1 << 20);   // elements per sub-chunk
   const size_t nchunks = (count + per_chunk - 1) / per_chunk;
-  const size_t want = (size_t)upload_lanes();
-  int nl = (int)(nchunks < want ? (nchunks ? nchunks : 1) : want);
+  const size_t want = on_device ? (size_t)upload_lanes() : (size_t)cvt_lanes(gpus);
+  const int nl = (int)(nchunks < want ? (nchunks ? nchunks : 1) : want);
+  lanes_init(fn, D, nl > 8 ? nl : 8);
   auto work = [&](int li) {
     cudaSetDevice(D.dev);
     Lane& L = D.lane[li];
@@ -395,10 +439,15 @@ void upload_f32_as_u8(const char* fn, Gpu& D, const float* src, size_t count, ui
       const int b = L.turn;
       L.turn ^= 1;
       if (L.used[b]) CU(fn, cudaEventSynchronize(L.done[b]));
-      memcpy(L.pin[b], src + off, n * 4);
-      float* dt = dtmp + ((size_t)li * 2 + b) * per_chunk;     // the device-side twin of pin[b]
-      CU(fn, cudaMemcpyAsync(dt, L.pin[b], n * 4, cudaMemcpyHostToDevice, L.copy));
-      CU(fn, f32_to_u8(dt, dst + off, n, L.copy));
+      if (on_device) {
+        memcpy(L.pin[b], src + off, n * 4);
+        float* dt = dtmp + ((size_t)li * 2 + b) * per_chunk;     // the device-side twin of pin[b]
+        CU(fn, cudaMemcpyAsync(dt, L.pin[b], n * 4, cudaMemcpyHostToDevice, L.copy));
+        CU(fn, f32_to_u8(dt, dst + off, n, L.copy));             // K0
+      } else {
+        f32_to_u8_host(src + off, static_cast<uint8_t*>(L.pin[b]), n);
+        CU(fn, cudaMemcpyAsync(dst + off, L.pin[b], n, cudaMemcpyHostToDevice, L.copy));
+      }
       CU(fn, cudaEventRecord(L.done[b], L.copy));
       L.used[b] = true;
     }
@@ -607,8 +656,10 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
   std::vector<float> hdict((size_t)n * dim * m);
   cascade_dictionary(cascade_seed(), dim, m, n, true, hdict.data());
   const char* fn = fn_;
-  // per GPU: its train shard and all query rows go up as float32 through the staging lanes, K0 turns each
-  // sub-chunk into uint8 as it lands, then K2-K4 on the shard with the SAME dictionary
+  const Trace tr;
+  tr("cascade: dictionary drawn");
+  // per GPU: its train shard and all query rows are converted to uint8 by the staging lanes' threads on their way
+  // into pinned memory (upload_f32_as_u8), then K2-K4 on the shard with the SAME dictionary
   per_gpu(c, [&](int gi) {
     Gpu& D = c.gpus[gi];
     CU(fn, cudaSetDevice(D.dev));
@@ -620,18 +671,21 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
     CU(fn, D.keys.ensure((size_t)2 * yrows * sizeof(unsigned long long)));
     CU(fn, D.dict.ensure(hdict.size() * 4));
     CU(fn, D.ws.ensure(wsb));
-    CU(fn, D.xf.ensure((size_t)NLANE * 2 * LANE_BYTES));   // device twins of the pinned staging buffers
+    CU(fn, D.xf.ensure((size_t)8 * 2 * LANE_BYTES));       // device twins of the pinned staging buffers (SPECTAVI_CVT=device)
     CU(fn, cudaMemcpyAsync(D.dict.p, hdict.data(), hdict.size() * 4, cudaMemcpyHostToDevice, D.stream));
     CU(fn, keys_reset((unsigned long long*)D.keys.p, yrows, D.stream));
     if (xn > 0) {
       CU(fn, D.x.ensure((size_t)xn * dim));
-      upload_f32_as_u8(fn, D, x + (size_t)x0 * dim, (size_t)xn * dim, (uint8_t*)D.x.p, (float*)D.xf.p);   // CascadingHashNn.h:236-239
+      upload_f32_as_u8(fn, D, x + (size_t)x0 * dim, (size_t)xn * dim, (uint8_t*)D.x.p, (float*)D.xf.p, (int)c.gpus.size());   // CascadingHashNn.h:236-239
     }
-    upload_f32_as_u8(fn, D, y, ybytes, (uint8_t*)D.y.p, (float*)D.xf.p);
+    tr("cascade: train rows queued", gi);
+    upload_f32_as_u8(fn, D, y, ybytes, (uint8_t*)D.y.p, (float*)D.xf.p, (int)c.gpus.size());
+    tr("cascade: query rows queued", gi);
     CU(fn, cascade_match((const uint8_t*)D.x.p, (const uint8_t*)D.y.p, xn, yrows, dim, m, n, g, (const float*)D.dict.p, 0,
                          (uint32_t)x0, (unsigned long long*)D.keys.p, D.ws.p, D.ws.cap, D.stream));
   });
   sync_all(fn_, c);        // hdict is about to go away; the collective below starts from quiescent streams
+  tr("cascade: K2-K4 done");
   merge_shards(fn_, c, yrows);
   if (ms) {
     deliver_matches(*ms, yrows, true);
@@ -646,6 +700,7 @@ void HostCall::cascade(const float* x, const float* y, int xrows, int yrows, int
   CU(fn_, cudaMemsetAsync(R.odist.p, 0, db, R.stream));
   CU(fn_, keys_finalize_f32((const unsigned long long*)R.keys.p, yrows, kcols, (uint64_t*)R.oidx.p, (float*)R.odist.p, R.stream));
   fetch_results(fn_, c, R, idx, R.oidx.p, ib, dist, R.odist.p, db);
+  tr("cascade: results delivered", (long long)ib, (long long)db);
 }
 
 // ---- single-GPU entry points: pageable <-> device without the driver's slow paths ----------------------------

@@ -85,4 +85,7 @@ class HostCall {
   int prev_dev_ = 0;                           // the caller's current device, restored on return
 };
 
+// K0 on the host (what nn_cascading_hash's staging threads run): K0's result bit for bit, any count
+void f32_to_u8_host(const float* in, uint8_t* out, size_t count);
+
 }  // namespace spv

@@ -1,3 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out; O=gpurun_out
-timeout 300 build/ubench_stage_mt > $O/n_stage_mt.txt 2>&1; cat $O/n_stage_mt.txt
+timeout 300 python tools/trace_cascade.py > $O/n_trace_cascade.txt 2>&1; grep -v "upload lane" $O/n_trace_cascade.txt
