@@ -19,3 +19,24 @@ for name, (x, y) in (("castle", (xu, yu)), ("uniform same shape", (rng.randint(0
     for _ in range(6):
         t0 = time.perf_counter(); feature.nn_bruteforcel1k2(x, y); t.append((time.perf_counter() - t0) * 1e3)
     print("   e2e ms", min(t))
+# where does a castle-sized launch lose time?  K1 alone against the train-row count (uniform bytes, 27 715 x 144 queries)
+print("sweep: xrows, K1 ms, ideal ms, ms above ideal")
+yq = torch.from_numpy(rng.randint(0, 256, yu.shape).astype("uint8")).cuda()
+for xr in (1734, 3469, 6938, 13876, 27753, 55506, 111012):
+    dx = torch.from_numpy(rng.randint(0, 256, (xr, xu.shape[1])).astype("uint8")).cuda()
+    keys = dev.new_keys(yq.shape[0], "cuda")
+    ms = []
+    for _ in range(6):
+        dev.keys_reset(keys); e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); dev.l1k2_fold(dx, yq, keys, 0); e1.record(); torch.cuda.synchronize(); ms.append(e0.elapsed_time(e1))
+    ideal = xr * yq.shape[0] * (xu.shape[1] / 4) / 18.2e12 * 1e3
+    print("  %7d  %.4f  %.4f  %.4f" % (xr, min(ms), ideal, min(ms) - ideal))
+# the same launch a second time WITHOUT resetting the keys: thresholds seeded, no candidate passes -> the cost of the slow path
+for name, x in (("castle", xu), ("uniform", rng.randint(0, 256, xu.shape).astype("uint8"))):
+    dx = torch.from_numpy(x).cuda(); dy = torch.from_numpy(yu if name == "castle" else yq.cpu().numpy()).cuda()
+    keys = dev.new_keys(dy.shape[0], "cuda"); dev.l1k2_fold(dx, dy, keys, 0)
+    ms = []
+    for _ in range(6):
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); dev.l1k2_fold(dx, dy, keys, 0); e1.record(); torch.cuda.synchronize(); ms.append(e0.elapsed_time(e1))
+    print(name, "second pass over the same rows (nothing to insert) ms", min(ms))
