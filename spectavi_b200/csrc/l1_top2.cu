@@ -161,13 +161,14 @@ __device__ __forceinline__ uint32_t thr_of(unsigned long long second) {
 // memory.  The 8 lanes that split a row's train columns share ONE pair per row, so
 // the row threshold is the true running 2nd-best (a per-lane pair would make it
 // about the 10th-best and the slow path 4x more frequent: ncu r01, 39 % of tiles).
-__device__ __noinline__ void offer(unsigned long long* best, uint32_t dist, uint32_t gidx) {
+__device__ __forceinline__ void offer_body(unsigned long long* best, uint32_t dist, uint32_t gidx) {
   const unsigned long long key = ((unsigned long long)dist << 32) | gidx;
   const unsigned long long old = atomicMin(best, key);
   if (old == key) return;   // the seeded best offered again (same train range folded twice)
   const unsigned long long loser = old > key ? old : key;
   if (loser != KEY_NONE) atomicMin(best + BY, loser);
 }
+__device__ __noinline__ void offer(unsigned long long* best, uint32_t dist, uint32_t gidx) { offer_body(best, dist, gidx); }
 
 // Half a k-chunk (8 dims) of the 8 x 8 register tile.  Operands are loaded by kload() one half-chunk AHEAD
 // of the ksad() that consumes them (two register sets of 16 x 8 B, the same 64 registers a whole chunk of
@@ -226,6 +227,9 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmy,
                const __grid_constant__ Params p) {
   extern __shared__ __align__(128) unsigned char smem[];
+#ifndef SPV_K1_OLD_SLOW
+  __shared__ uint4 slow_scr[NCW * 32 * 2];   // slow path: one 32-byte line per lane (8 accumulators of one query row)
+#endif
   const int nk16 = p.nk16, NST = p.nst;
   unsigned char* ytile = smem;
   unsigned char* xst = ytile + smem_ytile_bytes(nk16);
@@ -355,6 +359,58 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
     // tripped: a typical hit is one pair out of the warp's 2 048, and scanning all 64 accumulators of every
     // lane for it cost 3.4 % of the kernel (measured by disabling the slow path)
     const int anyneg = (rs[0] | rs[1] | rs[2] | rs[3]) | (rs[4] | rs[5] | rs[6] | rs[7]);
+#ifndef SPV_K1_OLD_SLOW
+    if (__any_sync(FULL, anyneg < 0)) {
+      // Slow path (rare): exact (dist, idx) insertion, then tighten the row thresholds.  Written for FEW INSTRUCTION
+      // CACHE LINES, not for few instructions: the code is cold every time it runs (the SAD loop owns the instruction
+      // cache), and the straightforward form -- 64 unrolled "accumulator negative? offer it" sites, 15 KB of code of
+      // which a visit touched ~27 lines -- cost 700-1500 cycles per visit (tools/castle_k1.py: 0.24 ms of a
+      // 27 k x 27 k launch, 1.9 % at C3).  Here the tripped rows are walked by a loop: the 8 lanes that share a query
+      // row agree on the row (mask OR-ed over the group), the lane's 8 accumulators of that row go to a per-lane
+      // scratch line by predicated stores (the only place the register tile needs a static index), a compact loop
+      // offers the negative ones, and only that row's threshold is re-read.
+      uint32_t m = 0;
+#pragma unroll
+      for (int i = 0; i < TY; ++i) m |= ((uint32_t)rs[i] >> 31) << i;
+      m |= __shfl_xor_sync(FULL, m, 1);
+      m |= __shfl_xor_sync(FULL, m, 2);
+      m |= __shfl_xor_sync(FULL, m, 4);
+      const uint32_t g0 = (uint32_t)(xt * BX + lx);
+      uint4* scr = slow_scr + (warp * 32 + lane) * 2;
+#pragma unroll 1
+      while (__any_sync(FULL, m != 0)) {
+        const int i = m ? __ffs(m) - 1 : TY;      // TY: this group has no row left, it idles through the round
+        m &= m - 1;
+        uint32_t nt = 0;
+#define SPV_ROW_OUT(k) case k: scr[0] = make_uint4(acc[k][0], acc[k][1], acc[k][2], acc[k][3]); \
+                               scr[1] = make_uint4(acc[k][4], acc[k][5], acc[k][6], acc[k][7]); nt = negthr[k]; break;
+        switch (i) { SPV_ROW_OUT(0) SPV_ROW_OUT(1) SPV_ROW_OUT(2) SPV_ROW_OUT(3) SPV_ROW_OUT(4) SPV_ROW_OUT(5) SPV_ROW_OUT(6) SPV_ROW_OUT(7) default: break; }
+#undef SPV_ROW_OUT
+        if (i < TY) {
+          const uint32_t thr = 0u - nt;
+          // the negative ones of the 8: a bit mask from the line just written, then one trip per candidate (the slow
+          // path's instructions compete with the SAD stream for the ALU pipe: ncu, a cold 27 k x 27 k launch issues
+          // 7.6 % more warp instructions than the same launch over seeded keys and runs 14 % longer)
+          const uint32_t* a = reinterpret_cast<const uint32_t*>(scr);
+          const uint4 a0 = scr[0], a1 = scr[1];
+          uint32_t cm = (a0.x >> 31) | ((a0.y >> 31) << 1) | ((a0.z >> 31) << 2) | ((a0.w >> 31) << 3) |
+                        ((a1.x >> 31) << 4) | ((a1.y >> 31) << 5) | ((a1.z >> 31) << 6) | ((a1.w >> 31) << 7);
+#pragma unroll 1
+          while (cm) {
+            const int j = __ffs(cm) - 1;
+            cm &= cm - 1;
+            const uint32_t lidx = g0 + 8 * j;
+            if (lidx < (uint32_t)p.xrows) offer_body(st + ly + 4 * i, a[j] + thr, p.xoffset + lidx);   // the one call site: inline
+          }
+        }
+        __syncwarp();
+        const uint32_t nn = i < TY ? 0u - thr_of(st[BY + ly + 4 * i]) : 0u;
+#define SPV_THR_IN(k) case k: negthr[k] = nn; break;
+        switch (i) { SPV_THR_IN(0) SPV_THR_IN(1) SPV_THR_IN(2) SPV_THR_IN(3) SPV_THR_IN(4) SPV_THR_IN(5) SPV_THR_IN(6) SPV_THR_IN(7) default: break; }
+#undef SPV_THR_IN
+      }
+    }
+#else
     if (__any_sync(FULL, anyneg < 0)) {
       // slow path (rare): exact (dist, idx) insertion, then tighten the row thresholds
       const uint32_t g0 = (uint32_t)(xt * BX + lx);
@@ -373,6 +429,7 @@ l1_top2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ 
 #pragma unroll
       for (int i = 0; i < TY; ++i) negthr[i] = 0u - thr_of(st[BY + ly + 4 * i]);
     }
+#endif
     if (++stage == NST) { stage = 0; phase ^= 1; }
     if (++xt == p.nxt) { xt = 0; ++yt; }
   }

@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out; O=gpurun_out
-timeout 900 python -m pytest tests/test_l1k2_gpu.py tests/test_castle_c2.py tests/test_ratio_gpu.py -m gpu -q -x > $O/n_pytest.log 2>&1; echo "rc=$?" >> $O/n_pytest.log; tail -3 $O/n_pytest.log
-for w in 0 1; do echo "SPECTAVI_K1_WARM=$w"; SPECTAVI_K1_WARM=$w timeout 300 python tools/castle_k1.py 2>&1; done > $O/n_castle_k1_warm.txt; cat $O/n_castle_k1_warm.txt
+timeout 120 python tools/k1_cold_vs_seeded.py > $O/n_plain.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:l1_top2_kernel -c 2 -f -o $O/k1_cold_seeded python tools/k1_cold_vs_seeded.py > $O/n_ncu.log 2>&1
+tail -3 $O/n_ncu.log; ls -la $O/k1_cold_seeded.ncu-rep
