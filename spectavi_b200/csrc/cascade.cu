@@ -418,6 +418,8 @@ __device__ __forceinline__ void hq_epilogue_table(uint32_t taddr, const int32_t*
       // the default probe depth (g = 2): both minima in ONE pass, 3 min / max per key
       // (VIMNMX issues at 5.6 T/s on this GPU against 18 T/s for other ALU ops -- pipe_peak.cu -- and this loop is what
       // keeps the query side ALU-bound; spelling it as setp + selp does not help: ptxas folds those back into VIMNMX)
+      // (also measured: the minimum by a tree of 3-input minima, knock-out by compare + select, second tree -- 24 VIMNMX3 +
+      // 48 full-rate ops instead of 72 VIMNMX for MP = 24 -- runs the query side at 97 us instead of 47: two live arrays of MP keys)
       uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
 #pragma unroll
       for (int b = 0; b < MP; ++b) {

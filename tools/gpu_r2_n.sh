@@ -1,4 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out; O=gpurun_out
-timeout 120 python tools/k1_cold_vs_seeded.py > $O/n_plain.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:l1_top2_kernel -c 2 -f -o $O/k1_cold_seeded python tools/k1_cold_vs_seeded.py > $O/n_ncu.log 2>&1
-tail -3 $O/n_ncu.log; ls -la $O/k1_cold_seeded.ncu-rep
+timeout 300 python tools/trace_e2e.py > $O/n_trace_e2e.txt 2>&1; grep -v "upload lane" $O/n_trace_e2e.txt | tail -45

@@ -1,12 +1,11 @@
 #!/bin/bash
+# same-box A/B of cascade variants: build/libspectavi_k2_<v>.so
 mkdir -p gpurun_out; O=gpurun_out
-: > $O/r_k4_variants.txt
-for rep in 1 2; do
-for v in PF1 PF2 PF4 PF8; do
-  SPECTAVI_B200_LIB=$PWD/build/libspectavi_k4_$v.so timeout 300 python tools/bench_cascade.py 1000000 128 5 0 2>/dev/null | python -c "
+timeout 600 python -m pytest tests/test_cascade_gpu.py tests/test_castle_c2.py -m gpu -q -x > $O/r_pytest.log 2>&1; echo "rc=$?" >> $O/r_pytest.log; tail -3 $O/r_pytest.log
+: > $O/r_k2_variants.txt
+for rep in 1 2; do for v in head tree; do
+  SPECTAVI_B200_LIB=$PWD/build/libspectavi_k2_$v.so timeout 300 python tools/bench_cascade.py 1000000 128 5 0 2>/dev/null | python -c "
 import json,sys
-d=json.loads(sys.stdin.read()); print('$v', 'cascade_ms %.4f' % d['cascade_ms'], 'K4 %.4f' % d['stages']['K4(probe + gather + re-rank)']['ms'])" >> $O/r_k4_variants.txt
-done
-done
-nvidia-smi --query-gpu=name,clocks.sm,clocks.mem,temperature.gpu,power.draw --format=csv >> $O/r_k4_variants.txt
-cat $O/r_k4_variants.txt
+d=json.loads(sys.stdin.read()); st=d['stages']; print('$v', 'cascade_ms %.4f' % d['cascade_ms'], 'K2train %.4f' % st['K2_train(projection + codes)']['ms'], 'K2query %.4f' % st['K2_query(+ least-confident bits)']['ms'], 'K4 %.4f' % st['K4(probe + gather + re-rank)']['ms'])" >> $O/r_k2_variants.txt
+done; done
+cat $O/r_k2_variants.txt
