@@ -1,9 +1,8 @@
 #!/bin/bash
 # same-box A/B of cascade variants: build/libspectavi_k2_<v>.so
 mkdir -p gpurun_out; O=gpurun_out
-timeout 600 python -m pytest tests/test_cascade_gpu.py tests/test_castle_c2.py -m gpu -q -x > $O/r_pytest.log 2>&1; echo "rc=$?" >> $O/r_pytest.log; tail -3 $O/r_pytest.log
 : > $O/r_k2_variants.txt
-for rep in 1 2; do for v in head tree; do
+for rep in 1 2; do for v in occ8 occ9 occ10; do
   SPECTAVI_B200_LIB=$PWD/build/libspectavi_k2_$v.so timeout 300 python tools/bench_cascade.py 1000000 128 5 0 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read()); st=d['stages']; print('$v', 'cascade_ms %.4f' % d['cascade_ms'], 'K2train %.4f' % st['K2_train(projection + codes)']['ms'], 'K2query %.4f' % st['K2_query(+ least-confident bits)']['ms'], 'K4 %.4f' % st['K4(probe + gather + re-rank)']['ms'])" >> $O/r_k2_variants.txt
